@@ -1,0 +1,79 @@
+"""The oracle (oracle/lassim_oracle.py) against the golden vectors produced by
+running the reference's own code (oracle/gen_golden.py).  CPU only."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import load_golden, REPO
+
+sys.path.insert(0, os.path.join(REPO, "oracle"))
+import lassim_oracle as orc  # noqa: E402
+
+
+def test_golden_files_hold_reference_outputs(th2, th2_uniform, th2_late):
+    assert th2["data"].shape == (6, 12) and th2["pert"].shape == (12, 14)
+    assert int(th2["mask"].sum()) == 63 == int(th2["react_count"])
+    assert th2_uniform["X"].shape[1] == 87
+    # the reference's own total is factor*pert + main (core_problem.py:155)
+    for g in (th2_uniform, th2_late):
+        f = float(g["pert_factor"])
+        np.testing.assert_allclose(
+            g["ref_total"], f * g["ref_pert_cost"] + g["ref_cost_main"],
+            rtol=1e-14)
+    # values recorded in SURVEY.md Appendix A for default_rng(0) candidates
+    np.testing.assert_allclose(th2_uniform["ref_cost_main"][:3],
+                               [368.665, 280.746, 273.432], rtol=1e-5)
+
+
+@pytest.mark.parametrize("name,count", [("th2_uniform", 6), ("th2_late", 6)])
+def test_oracle_reproduces_reference_costs(th2, name, count):
+    g = load_golden(name)
+    p = th2
+    for i in range(count):
+        tot, c, pc = orc.total_cost(g["X"][i], p["data"], p["sigma"],
+                                    p["times"], p["y0"], p["pert"],
+                                    float(g["pert_factor"]), p["vector_map"],
+                                    p["mask"])
+        # same LSODA, same arithmetic: equal to rounding
+        assert c == pytest.approx(g["ref_cost_main"][i], rel=1e-12)
+        assert pc == pytest.approx(g["ref_pert_cost"][i], rel=1e-9)
+        assert tot == pytest.approx(g["ref_total"][i], rel=1e-10)
+
+
+def test_oracle_trajectories_match_reference(th2, th2_uniform):
+    p, g = th2, th2_uniform
+    for i in range(4):
+        Y = orc.odeint_lassim(p["y0"], p["times"], g["X"][i], p["vector_map"],
+                              p["mask"], 12)
+        np.testing.assert_allclose(Y, g["ref_Y"][i], rtol=1e-12, atol=1e-300)
+
+
+def test_generated_file_stored_port_equals_reference():
+    for name in ("th2_uniform", "th2_late", "syn50"):
+        g = load_golden(name)
+        np.testing.assert_allclose(g["port_cost_main"], g["ref_cost_main"],
+                                   rtol=1e-12)
+        np.testing.assert_allclose(g["port_pert_cost"], g["ref_pert_cost"],
+                                   rtol=1e-9)
+
+
+def test_rank1_residual_closed_form():
+    rng = np.random.default_rng(3)
+    r = rng.normal(size=144)
+    p = rng.normal(size=144)
+    closed = p @ p - (r @ p) ** 2 / (r @ r)
+    assert orc.rank1_residual(r, p) == pytest.approx(closed, rel=1e-12)
+
+
+def test_reference_functions_load_when_built(th2, th2_uniform):
+    fns = orc.load_reference_functions()
+    if fns is None:
+        pytest.skip("oracle/_ref not built (no /root/reference on this box)")
+    p, g = th2, th2_uniform
+    tot, c, pc = orc.reference_total_cost(
+        g["X"][0], p["data"], p["sigma"], p["times"], p["y0"], p["pert"],
+        float(g["pert_factor"]), p["vector_map"], p["mask"], fns)
+    assert c == pytest.approx(g["ref_cost_main"][0], rel=1e-13)
+    assert tot == pytest.approx(g["ref_total"][0], rel=1e-12)
