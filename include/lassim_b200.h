@@ -1,0 +1,145 @@
+/*
+ * lassim_b200 - C ABI of the B200 cost-evaluation engine for LASSIM core
+ * problems.  This is the drop-in boundary: plain pointers and sizes, FP64,
+ * row-major, caller-owned buffers, no exceptions, no torch types.
+ *
+ * Every entry point returns 0 on success and a negative LASSIM_E_* code on
+ * failure; lassim_last_error() gives the message of the last failure on that
+ * handle (or of the last failed lassim_create when called with NULL).
+ *
+ * A handle belongs to one (process, device).  It is not thread-safe.  Calls
+ * block until their results are in the caller's buffers unless the name ends
+ * in _device (those enqueue on the given stream and return).
+ *
+ * Reference interfaces replaced (paths in gmariotti/lassim):
+ *   source/core/functions/common_functions.pxd:17-23        ode plugin
+ *   source/core/functions/perturbation_functions.pxd:10-14  knock-down plugin
+ *   source/core/core_problem.py:75-92, 134-155              _objfun_impl
+ *   source/core/core_problem.py:189-245                     factory / build
+ */
+#ifndef LASSIM_B200_H
+#define LASSIM_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct lassim_handle lassim_handle;
+
+enum {
+    LASSIM_OK = 0,
+    LASSIM_E_INVALID = -1,   /* bad argument (NULL, size, shape)            */
+    LASSIM_E_CUDA = -2,      /* a CUDA runtime call failed                  */
+    LASSIM_E_STATE = -3,     /* call order (no problem set, ...)            */
+    LASSIM_E_UNSUPPORTED = -4 /* problem size outside what the kernels cover */
+};
+
+/* Per-candidate status written by the evaluation (bit field, 0 = ok). */
+enum {
+    LASSIM_ST_OK = 0,
+    LASSIM_ST_STEP_BUDGET = 1, /* a trajectory used max_steps step attempts */
+    LASSIM_ST_NONFINITE = 2    /* step size underflow / non-finite state    */
+};
+
+/* Library version, "major.minor.patch". */
+const char *lassim_version(void);
+
+/* Create / destroy an engine on CUDA device `device`. */
+int lassim_create(int device, lassim_handle **out);
+int lassim_destroy(lassim_handle *h);
+const char *lassim_last_error(const lassim_handle *h);
+
+/*
+ * Problem constants; replaces CoreProblemFactory.new_instance + build
+ * (source/core/core_problem.py:168-187, 219-245).
+ *   n        number of transcription factors (state size)
+ *   T        number of sample times, times[0] is the start (state = y0)
+ *   times[T], y0[n], data[T*n] (row = sample time), sigma[n]
+ *   mask[n*n] row-major, non-zero where gene `row` is regulated by gene `col`
+ *            (the reference's vector_map_mask, source/customs/
+ *            core_functions.py:38-60); the True entries in row-major order are
+ *            the order of the k values in a decision vector
+ *   pert     NULL, or [n*(n+2)]: n x n knock-down matrix followed by t_start,
+ *            t_end per row (perturbation_functions.pyx:46-49)
+ *   pert_factor  weight of the knock-down cost in the total
+ * Decision vector layout: x = [lambda(n) | vmax(n) | k(nnz)], dim = 2n + nnz
+ * (common_functions.pyx:80-82).
+ */
+int lassim_set_problem(lassim_handle *h, int n, int T, const double *times,
+                       const double *y0, const double *data,
+                       const double *sigma, const unsigned char *mask,
+                       const double *pert, double pert_factor);
+
+/* Replace only the regulation mask (each edge-pruning iteration rebuilds it,
+ * source/customs/core_functions.py:101-120).  dim becomes 2n + popcount. */
+int lassim_set_mask(lassim_handle *h, const unsigned char *mask);
+
+/* Integrator controls.  Defaults mirror scipy.integrate.odeint as the
+ * reference calls it (common_functions.pyx:86-90): rtol = atol = 1.49012e-8,
+ * error weight rtol*|y| + atol, max-norm.  max_steps bounds the step attempts
+ * of one trajectory (default 20,000,000; the reference's mxstep=1e8 would let
+ * one candidate hold a GPU for minutes). */
+int lassim_set_tolerances(lassim_handle *h, double rtol, double atol,
+                          long long max_steps);
+
+/* Current decision-vector length (2n + nnz), trajectories per candidate
+ * (1 + unique time pairs + n when a knock-down matrix is set, else 1). */
+int lassim_dim(const lassim_handle *h);
+int lassim_trajectories_per_candidate(const lassim_handle *h);
+
+/*
+ * Evaluate N candidates.  X[N*dim] in HOST memory; outputs in host memory.
+ * cost[N] = pert_factor * pert_cost + cost_main  (core_problem.py:155).
+ * Optional (may be NULL): cost_main[N], pert_cost[N], status[N],
+ * counters[N*3] = {accepted steps, rejected steps, RHS evaluations} summed
+ * over the candidate's trajectories.
+ * Replaces N calls of CoreWithPerturbationsProblem._objfun_impl
+ * (core_problem.py:134-155) / CoreProblem._objfun_impl (:75-92).
+ */
+int lassim_eval(lassim_handle *h, int N, const double *X, double *cost,
+                double *cost_main, double *pert_cost, int *status,
+                unsigned long long *counters);
+
+/* Same, with X and every non-NULL output in DEVICE memory, enqueued on
+ * `stream` (a cudaStream_t passed as void*; NULL = the handle's own stream).
+ * Returns after the launch; synchronise the stream before reading. */
+int lassim_eval_device(lassim_handle *h, int N, const double *dX, double *dcost,
+                       double *dcost_main, double *dpert_cost, int *dstatus,
+                       unsigned long long *dcounters, void *stream);
+
+/*
+ * Time-series trajectories at the sample times: Y[N*T*n] (host), Y[c][0] = y0.
+ * Replaces the ode plugin odeint1e8_lassim (common_functions.pyx:55-90) for a
+ * batch; status[N] optional.
+ */
+int lassim_trajectories(lassim_handle *h, int N, const double *X, double *Y,
+                        int *status);
+
+/*
+ * End states of the knock-down part of the LAST lassim_eval / _eval_device
+ * call: E[N*K*n], K = lassim_trajectories_per_candidate(); slot 0 is unused
+ * (time series), 1..U the controls in order of first appearance, 1+U+i the
+ * knocked system of row i (perturbation_functions.pyx:64-85).  For tests and
+ * diagnostics.
+ */
+int lassim_last_end_states(lassim_handle *h, int N, double *E);
+
+/* Step attempts per trajectory of the LAST evaluation: steps[N*K]. */
+int lassim_last_traj_steps(lassim_handle *h, int N, unsigned int *steps);
+
+/* Number of kernels this handle has launched so far. */
+long long lassim_launch_count(const lassim_handle *h);
+
+/* Device time of the last evaluation kernel in milliseconds (CUDA events on
+ * the launching stream); blocks until that kernel has finished. */
+int lassim_last_kernel_ms(lassim_handle *h, float *ms);
+
+/* FP64 FMA throughput probe: runs a register-resident DFMA kernel for about
+ * `iters` dependent FMAs per thread and returns achieved TFLOP/s (2 flops per
+ * FMA).  Used as the roofline denominator (no reference counterpart). */
+int lassim_fp64_peak_probe(lassim_handle *h, int iters, double *tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LASSIM_B200_H */

@@ -1,0 +1,242 @@
+"""ctypes binding of liblassim_b200.so (include/lassim_b200.h).
+
+There is no CPU fallback: if the shared library is missing or a CUDA call
+fails, these functions raise."""
+import ctypes
+import os
+
+import numpy as np
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_PKG, "liblassim_b200.so")
+_lib = None
+
+c_double_p = ctypes.POINTER(ctypes.c_double)
+c_int_p = ctypes.POINTER(ctypes.c_int)
+c_uint_p = ctypes.POINTER(ctypes.c_uint)
+c_ubyte_p = ctypes.POINTER(ctypes.c_ubyte)
+c_ull_p = ctypes.POINTER(ctypes.c_ulonglong)
+
+ST_STEP_BUDGET = 1
+ST_NONFINITE = 2
+
+
+class LassimError(RuntimeError):
+    pass
+
+
+def library_path():
+    return _LIB_PATH
+
+
+def load_library():
+    """Load liblassim_b200.so (built in-tree by lassim_b200.build)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB_PATH):
+        raise LassimError(
+            "liblassim_b200.so is not built (%s); run `python -m "
+            "lassim_b200.build` - there is no CPU fallback" % _LIB_PATH)
+    lib = ctypes.CDLL(_LIB_PATH)
+    H = ctypes.c_void_p
+    lib.lassim_version.restype = ctypes.c_char_p
+    lib.lassim_last_error.restype = ctypes.c_char_p
+    lib.lassim_last_error.argtypes = [H]
+    lib.lassim_create.argtypes = [ctypes.c_int, ctypes.POINTER(H)]
+    lib.lassim_destroy.argtypes = [H]
+    lib.lassim_set_problem.argtypes = [H, ctypes.c_int, ctypes.c_int, c_double_p,
+                                       c_double_p, c_double_p, c_double_p,
+                                       c_ubyte_p, c_double_p, ctypes.c_double]
+    lib.lassim_set_mask.argtypes = [H, c_ubyte_p]
+    lib.lassim_set_tolerances.argtypes = [H, ctypes.c_double, ctypes.c_double,
+                                          ctypes.c_longlong]
+    lib.lassim_dim.argtypes = [H]
+    lib.lassim_trajectories_per_candidate.argtypes = [H]
+    lib.lassim_eval.argtypes = [H, ctypes.c_int, c_double_p, c_double_p,
+                                c_double_p, c_double_p, c_int_p, c_ull_p]
+    lib.lassim_eval_device.argtypes = [H, ctypes.c_int, ctypes.c_void_p,
+                                       ctypes.c_void_p, ctypes.c_void_p,
+                                       ctypes.c_void_p, ctypes.c_void_p,
+                                       ctypes.c_void_p, ctypes.c_void_p]
+    lib.lassim_trajectories.argtypes = [H, ctypes.c_int, c_double_p, c_double_p,
+                                        c_int_p]
+    lib.lassim_last_end_states.argtypes = [H, ctypes.c_int, c_double_p]
+    lib.lassim_last_traj_steps.argtypes = [H, ctypes.c_int, c_uint_p]
+    lib.lassim_launch_count.argtypes = [H]
+    lib.lassim_launch_count.restype = ctypes.c_longlong
+    lib.lassim_last_kernel_ms.argtypes = [H, ctypes.POINTER(ctypes.c_float)]
+    lib.lassim_fp64_peak_probe.argtypes = [H, ctypes.c_int, c_double_p]
+    for name in ("lassim_create", "lassim_destroy", "lassim_set_problem",
+                 "lassim_set_mask", "lassim_set_tolerances", "lassim_dim",
+                 "lassim_trajectories_per_candidate", "lassim_eval",
+                 "lassim_eval_device", "lassim_trajectories",
+                 "lassim_last_end_states", "lassim_last_traj_steps",
+                 "lassim_last_kernel_ms", "lassim_fp64_peak_probe"):
+        getattr(lib, name).restype = ctypes.c_int
+    _lib = lib
+    return lib
+
+
+def _dp(a):
+    return a.ctypes.data_as(c_double_p)
+
+
+def _f64(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    if shape is not None and a.shape != shape:
+        raise ValueError("expected shape %s, got %s" % (shape, a.shape))
+    return a
+
+
+class Engine:
+    """One evaluation engine on one CUDA device (a lassim_handle)."""
+
+    def __init__(self, device=0):
+        self._lib = load_library()
+        self._h = ctypes.c_void_p()
+        rc = self._lib.lassim_create(int(device), ctypes.byref(self._h))
+        if rc != 0:
+            msg = self._lib.lassim_last_error(None).decode()
+            self._h = None
+            raise LassimError("lassim_create(device=%d) failed: %s" % (device, msg))
+        self.device = int(device)
+        self.n = self.T = 0
+
+    # -- plumbing ----------------------------------------------------------
+    def _check(self, rc, what):
+        if rc != 0:
+            raise LassimError("%s failed (%d): %s" % (
+                what, rc, self._lib.lassim_last_error(self._h).decode()))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.lassim_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- problem -----------------------------------------------------------
+    def set_problem(self, data, sigma, times, y0, mask, pert=None, pert_factor=0.0):
+        y0 = _f64(y0).reshape(-1)
+        n = y0.size
+        times = _f64(times).reshape(-1)
+        T = times.size
+        data = _f64(data)
+        if data.shape != (T, n):
+            raise ValueError("data shape %s is not (T=%d, n=%d)" % (data.shape, T, n))
+        sigma = _f64(np.broadcast_to(_f64(sigma), (n,)))
+        mask = np.ascontiguousarray(np.asarray(mask).reshape(-1) != 0, dtype=np.uint8)
+        if mask.size != n * n:
+            raise ValueError("mask has %d entries, expected n*n=%d" % (mask.size, n * n))
+        pp = None
+        if pert is not None:
+            pert = _f64(pert)
+            if pert.shape != (n, n + 2):
+                raise ValueError("perturbation data shape %s is not (n, n+2)=(%d, %d)"
+                                 % (pert.shape, n, n + 2))
+            pp = _dp(pert)
+        self._check(self._lib.lassim_set_problem(
+            self._h, n, T, _dp(times), _dp(y0), _dp(data), _dp(sigma),
+            mask.ctypes.data_as(c_ubyte_p), pp, float(pert_factor)), "lassim_set_problem")
+        self.n, self.T = n, T
+
+    def set_mask(self, mask):
+        mask = np.ascontiguousarray(np.asarray(mask).reshape(-1) != 0, dtype=np.uint8)
+        if mask.size != self.n * self.n:
+            raise ValueError("mask has %d entries, expected %d" % (mask.size, self.n ** 2))
+        self._check(self._lib.lassim_set_mask(self._h, mask.ctypes.data_as(c_ubyte_p)),
+                    "lassim_set_mask")
+
+    def set_tolerances(self, rtol=1.49012e-8, atol=1.49012e-8, max_steps=20000000):
+        self._check(self._lib.lassim_set_tolerances(self._h, rtol, atol, int(max_steps)),
+                    "lassim_set_tolerances")
+
+    @property
+    def dim(self):
+        return self._lib.lassim_dim(self._h)
+
+    @property
+    def trajectories_per_candidate(self):
+        return self._lib.lassim_trajectories_per_candidate(self._h)
+
+    # -- evaluation ----------------------------------------------------------
+    def eval(self, X, details=False):
+        """cost[N] for host X[N, dim].  details=True returns a dict with
+        cost, cost_main, pert_cost, status, counters."""
+        X = _f64(X)
+        if X.ndim == 1:
+            X = X.reshape(1, -1)
+        N = X.shape[0]
+        if X.shape[1] != self.dim:
+            raise ValueError("decision vectors have %d entries, problem dimension is %d"
+                             % (X.shape[1], self.dim))
+        cost = np.empty(N)
+        if not details:
+            self._check(self._lib.lassim_eval(self._h, N, _dp(X), _dp(cost), None, None,
+                                              None, None), "lassim_eval")
+            return cost
+        cm = np.empty(N); pc = np.empty(N)
+        st = np.empty(N, dtype=np.int32)
+        cnt = np.empty((N, 3), dtype=np.uint64)
+        self._check(self._lib.lassim_eval(
+            self._h, N, _dp(X), _dp(cost), _dp(cm), _dp(pc),
+            st.ctypes.data_as(c_int_p), cnt.ctypes.data_as(c_ull_p)), "lassim_eval")
+        return dict(cost=cost, cost_main=cm, pert_cost=pc, status=st, counters=cnt)
+
+    def eval_device(self, N, x_ptr, cost_ptr, cost_main_ptr=None, pert_cost_ptr=None,
+                    status_ptr=None, counters_ptr=None, stream=None):
+        """Device-resident evaluation: raw device addresses (ints), enqueued on
+        `stream` (a cudaStream_t address; None = the engine's stream)."""
+        self._check(self._lib.lassim_eval_device(
+            self._h, int(N), x_ptr, cost_ptr, cost_main_ptr, pert_cost_ptr,
+            status_ptr, counters_ptr, stream), "lassim_eval_device")
+
+    def trajectories(self, X, return_status=False):
+        X = _f64(X)
+        if X.ndim == 1:
+            X = X.reshape(1, -1)
+        N = X.shape[0]
+        if X.shape[1] != self.dim:
+            raise ValueError("decision vectors have %d entries, problem dimension is %d"
+                             % (X.shape[1], self.dim))
+        Y = np.empty((N, self.T, self.n))
+        st = np.empty(N, dtype=np.int32)
+        self._check(self._lib.lassim_trajectories(self._h, N, _dp(X), _dp(Y),
+                                                  st.ctypes.data_as(c_int_p)),
+                    "lassim_trajectories")
+        return (Y, st) if return_status else Y
+
+    def last_end_states(self, N):
+        K = self.trajectories_per_candidate
+        E = np.empty((N, K, self.n))
+        self._check(self._lib.lassim_last_end_states(self._h, N, _dp(E)),
+                    "lassim_last_end_states")
+        return E
+
+    def last_traj_steps(self, N):
+        K = self.trajectories_per_candidate
+        s = np.empty((N, K), dtype=np.uint32)
+        self._check(self._lib.lassim_last_traj_steps(self._h, N, s.ctypes.data_as(c_uint_p)),
+                    "lassim_last_traj_steps")
+        return s
+
+    @property
+    def launch_count(self):
+        return int(self._lib.lassim_launch_count(self._h))
+
+    def last_kernel_ms(self):
+        ms = ctypes.c_float()
+        self._check(self._lib.lassim_last_kernel_ms(self._h, ctypes.byref(ms)),
+                    "lassim_last_kernel_ms")
+        return float(ms.value)
+
+    def fp64_peak_tflops(self, iters=200000):
+        v = ctypes.c_double()
+        self._check(self._lib.lassim_fp64_peak_probe(self._h, int(iters), ctypes.byref(v)),
+                    "lassim_fp64_peak_probe")
+        return float(v.value)

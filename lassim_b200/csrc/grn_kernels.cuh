@@ -1,0 +1,546 @@
+// Device side of the LASSIM cost evaluation for sm_100a.
+//
+// One lane group (G lanes of a warp, R genes per lane, G*R >= n) integrates one
+// (candidate, trajectory) pair with an FP64 adaptive Dormand-Prince 5(4) method
+// whose error control mirrors the reference integrator's: error weight
+// rtol*|y| + atol, max-norm, rtol = atol = 1.49012e-8 by default (the reference
+// calls scipy.integrate.odeint = ODEPACK LSODA with its defaults,
+// source/core/functions/common_functions.pyx:86-90).
+//
+// Per lane, in registers: its R state entries, the seven stage derivatives,
+// lambda, vmax and its R dense rows of W.  The stage state is exchanged through
+// a double-buffered shared-memory line per group (one __syncwarp per RHS
+// evaluation, conflict-free 16-byte broadcast loads).  Groups pull work items
+// from a global atomic queue, so a warp keeps all of its groups busy although
+// step counts differ by orders of magnitude between trajectories.
+//
+// Fused reductions: the time-series cost (core_problem.py:89-90) is computed by
+// the group that integrated the time series; the knock-down cost
+// (perturbation_functions.pyx:82-102) by whichever group finishes a candidate's
+// last trajectory (arrival counter + __threadfence).
+#pragma once
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+namespace lassim {
+
+struct DevProblem {
+    int n, T, K, U, dim, nnz;
+    const double *times;      // [T]
+    const double *y0;         // [n]
+    const double *data;       // [T*n]
+    const double *sigma2;     // [n]
+    const int *kidx;          // [n*n] index into the k part of x, or -1
+    const double *pert;       // [n*(n+2)] or nullptr
+    const int *traj_prefix;   // [K] rows whose lambda is already scaled
+    const double *traj_tt;    // [K*2] start / end time (slot 0 unused)
+    const int *knock_ctrl;    // [n] trajectory index of row i's control
+    double pert_factor, rtol, atol;
+    unsigned int max_steps;
+};
+
+struct DevBatch {
+    int N;
+    int mode;                 // 0: all K trajectories + costs; 1: time series only
+    const double *X;          // [N*dim]
+    double *cost;             // [N]
+    double *cost_main;        // [N]
+    double *pert_cost;        // [N]
+    int *status;              // [N]   zeroed before launch
+    unsigned long long *counters;  // [N*3] zeroed before launch
+    double *Y;                // [N*T*n]
+    double *E;                // [N*K*n]
+    unsigned int *traj_steps; // [N*K]
+    int *done;                // [N]   zeroed before launch
+    unsigned int *work_counter;    // zeroed before launch
+    const unsigned int *order;     // optional permutation of work items
+};
+
+// Dormand-Prince 5(4) tableau.
+#define DP_A21 (1.0 / 5.0)
+#define DP_A31 (3.0 / 40.0)
+#define DP_A32 (9.0 / 40.0)
+#define DP_A41 (44.0 / 45.0)
+#define DP_A42 (-56.0 / 15.0)
+#define DP_A43 (32.0 / 9.0)
+#define DP_A51 (19372.0 / 6561.0)
+#define DP_A52 (-25360.0 / 2187.0)
+#define DP_A53 (64448.0 / 6561.0)
+#define DP_A54 (-212.0 / 729.0)
+#define DP_A61 (9017.0 / 3168.0)
+#define DP_A62 (-355.0 / 33.0)
+#define DP_A63 (46732.0 / 5247.0)
+#define DP_A64 (49.0 / 176.0)
+#define DP_A65 (-5103.0 / 18656.0)
+#define DP_B1 (35.0 / 384.0)
+#define DP_B3 (500.0 / 1113.0)
+#define DP_B4 (125.0 / 192.0)
+#define DP_B5 (-2187.0 / 6784.0)
+#define DP_B6 (11.0 / 84.0)
+#define DP_E1 (71.0 / 57600.0)
+#define DP_E3 (-71.0 / 16695.0)
+#define DP_E4 (71.0 / 1920.0)
+#define DP_E5 (-17253.0 / 339200.0)
+#define DP_E6 (22.0 / 525.0)
+#define DP_E7 (-1.0 / 40.0)
+
+constexpr int kThreads = 128;
+
+template <int G>
+__device__ __forceinline__ double group_max(double v, unsigned gmask) {
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1)
+        v = fmax(v, __shfl_xor_sync(gmask, v, o, G));
+    return v;
+}
+
+template <int G>
+__device__ __forceinline__ double group_sum(double v, unsigned gmask) {
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1)
+        v += __shfl_xor_sync(gmask, v, o, G);
+    return v;
+}
+
+// 2^(j/64), j = 0..63, filled by the host at load time.
+__constant__ double c_exp2_table[64];
+
+constexpr double kNegLog2e = -1.4426950408889634074;
+
+// Exact-libm activation vmax / (1 + exp(-z)) with the reference's overflow
+// behaviour: exp(-z) -> +inf gives 0 (common_functions.pyx:37-39).  Kept as the
+// A/B check of the fast path below (LASSIM_EXACT_MATH=1).
+__device__ __forceinline__ double logistic_libm(double z) {
+    return 1.0 / (1.0 + exp(-z));
+}
+
+// 1 / (1 + 2^t), t = -z*log2(e).  2^t = 2^n * T[j] * 2^f with t = n + j/64 + f,
+// |f| <= 2^-7 (degree-5 Taylor for 2^f - 1, truncation 4e-17); the reciprocal
+// is an SFU seed (MUFU.RCP64H) refined by two FP64 Newton steps.  ~3 ulp.  t is
+// clamped to +-1000: below, 2^t vanishes next to 1; above, the result is
+// < 1e-301 where the reference returns vmax*exp(z) or 0 after overflow.
+__device__ __forceinline__ double logistic_exp2(double t, const double *tab) {
+    t = fmin(fmax(t, -1000.0), 1000.0);
+    const double kMagic = 105553116266496.0;   // 1.5 * 2^46: ulp = 1/64
+    const double s = t + kMagic;
+    const int ki = __double2loint(s);
+    const double f = t - (s - kMagic);
+    const double tj = tab[ki & 63];
+    const double f2 = f * f;
+    const double p01 = fma(0.2402265069591007, f, 0.6931471805599453);
+    const double p23 = fma(0.009618129107628477, f, 0.05550410866482158);
+    const double p = fma(f2, fma(f2, 0.0013333558146428443, p23), p01);
+    const double v = fma(tj, f * p, tj);
+    const double e = __hiloint2double(__double2hiint(v) + ((ki >> 6) << 20),
+                                      __double2loint(v));
+    const double d = 1.0 + e;
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    r = fma(r, fma(-d, r, 1.0), r);
+    r = fma(r, fma(-d, r, 1.0), r);
+    return r;
+}
+
+// f = -lambda*ys + vmax*sigmoid(W ys); ys of the whole group goes through buf.
+// With FAST the rows of W arrive pre-scaled by -log2(e).  NC = columns of W
+// actually used (n rounded up to 4).
+template <int G, int R, int NC, bool FAST>
+__device__ __forceinline__ void rhs_eval(const double (&ys)[R], double (&f)[R],
+                                         const double (&W)[R][NC],
+                                         const double (&lam)[R],
+                                         const double (&vm)[R], double *buf,
+                                         const double *tab, unsigned gmask,
+                                         int lg) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) buf[lg * R + r] = ys[r];
+    __syncwarp(gmask);
+    double a0[R], a1[R], a2[R], a3[R], ly[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        a0[r] = 0.0; a1[r] = 0.0; a2[r] = 0.0; a3[r] = 0.0;
+        ly[r] = -lam[r] * ys[r];
+    }
+#pragma unroll
+    for (int j = 0; j < NC; j += 4) {
+        const double2 v = *reinterpret_cast<const double2 *>(buf + j);
+        const double2 u = *reinterpret_cast<const double2 *>(buf + j + 2);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            a0[r] = fma(W[r][j], v.x, a0[r]);
+            a1[r] = fma(W[r][j + 1], v.y, a1[r]);
+            a2[r] = fma(W[r][j + 2], u.x, a2[r]);
+            a3[r] = fma(W[r][j + 3], u.y, a3[r]);
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const double z = (a0[r] + a1[r]) + (a2[r] + a3[r]);
+        const double sg = FAST ? logistic_exp2(z, tab) : logistic_libm(z);
+        f[r] = fma(vm[r], sg, ly[r]);
+    }
+}
+
+// Max over the lanes of `gmask` of a non-negative double (NaN -> +inf), through
+// one REDUX on the float bit pattern (IEEE order = unsigned order for >= 0).
+__device__ __forceinline__ float group_max_nonneg(double q, unsigned gmask) {
+    float qf = (float)q;
+    if (!(q <= 3.0e38)) qf = CUDART_INF_F;   // NaN, inf or beyond float range
+    return __uint_as_float(__reduce_max_sync(gmask, __float_as_uint(qf)));
+}
+
+template <int G, int R, int NC, bool FAST>
+__global__ void __launch_bounds__(kThreads)
+grn_cost_kernel(const DevProblem P, const DevBatch B) {
+    constexpr int NP = G * R;
+    constexpr int STRIDE = NP + 2;   // 16 B skew between groups: no bank conflicts
+    constexpr int GPW = 32 / G;
+    static_assert(NC <= NP && NC % 4 == 0, "NC must be a multiple of 4 within G*R");
+    extern __shared__ double smem[];
+
+    const int lane = threadIdx.x & 31;
+    const int lg = lane % G;
+    const int gw = lane / G;
+    const unsigned gmask =
+        (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (gw * G));
+    const int gid = (threadIdx.x >> 5) * GPW + gw;
+    double *tab = smem;
+    double *ybuf = smem + 64 + gid * (2 * STRIDE);
+    if (threadIdx.x < 64) tab[threadIdx.x] = c_exp2_table[threadIdx.x];
+    for (int i = lg; i < 2 * STRIDE; i += G) ybuf[i] = 0.0;
+    __syncthreads();
+
+    const int n = P.n;
+    const int Kc = (B.mode == 0) ? P.K : 1;
+    const unsigned total_work = (unsigned)B.N * (unsigned)Kc;
+    const double rtol = P.rtol, atol = P.atol;
+
+    double y[R], k1[R], k2[R], k3[R], k4[R], k5[R], k6[R], k7[R], yn[R], ys[R];
+    double lam[R], vm[R], W[R][NC];
+    bool gene_ok[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) gene_ok[r] = (lg * R + r) < n;
+
+    bool active = false, exhausted = false;
+    int c = 0, k = 0, ti = 1, nt = 2, cur = 0, st = 0;
+    unsigned nacc = 0, nrej = 0;
+    bool rejected = false;
+    double t = 0.0, h = 0.0, tend = 0.0;
+    const double *tl = P.times;
+
+#define LASSIM_RHS(in, out)                                                    \
+    do {                                                                       \
+        rhs_eval<G, R, NC, FAST>(in, out, W, lam, vm, ybuf + cur * STRIDE,     \
+                                 tab, gmask, lg);                              \
+        cur ^= 1;                                                              \
+    } while (0)
+
+    while (true) {
+        if (!active && !exhausted) {
+            unsigned w = 0;
+            if (lg == 0) w = atomicAdd(B.work_counter, 1u);
+            w = __shfl_sync(gmask, w, 0, G);
+            if (w >= total_work) {
+                exhausted = true;
+            } else {
+                if (B.order != nullptr) w = B.order[w];
+                k = (int)(w / (unsigned)B.N);
+                c = (int)(w - (unsigned)k * (unsigned)B.N);
+                const double *x = B.X + (size_t)c * P.dim;
+                const int prefix = P.traj_prefix[k];
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const int g = lg * R + r;
+                    lam[r] = 0.0; vm[r] = 0.0; y[r] = 0.0;
+                    if (gene_ok[r]) {
+                        double l = x[g];
+                        if (g < prefix) l *= P.pert[(size_t)g * (n + 2) + g];
+                        lam[r] = l;
+                        vm[r] = x[n + g];
+                        y[r] = P.y0[g];
+                    }
+#pragma unroll
+                    for (int j = 0; j < NC; ++j) {
+                        double wv = 0.0;
+                        if (gene_ok[r] && j < n) {
+                            const int id = P.kidx[g * n + j];
+                            if (id >= 0) wv = x[2 * n + id];
+                        }
+                        W[r][j] = FAST ? wv * kNegLog2e : wv;
+                    }
+                }
+                if (k == 0) { tl = P.times; nt = P.T; }
+                else { tl = P.traj_tt + 2 * k; nt = 2; }
+                t = tl[0];
+                ti = 1;
+                tend = (nt > 1) ? tl[1] : t;
+                nacc = 0; nrej = 0; rejected = false; st = 0;
+                if (k == 0) {
+                    double *Yc = B.Y + (size_t)c * P.T * n;
+#pragma unroll
+                    for (int r = 0; r < R; ++r)
+                        if (gene_ok[r]) Yc[lg * R + r] = y[r];
+                }
+                // first derivative + starting step (Hairer/Norsett/Wanner II.4,
+                // max-norm variant)
+                LASSIM_RHS(y, k1);
+                double d0 = 0.0, d1 = 0.0;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const double sc = fma(rtol, fabs(y[r]), atol);
+                    d0 = fmax(d0, fabs(y[r]) / sc);
+                    d1 = fmax(d1, fabs(k1[r]) / sc);
+                }
+                d0 = group_max<G>(d0, gmask);
+                d1 = group_max<G>(d1, gmask);
+                const double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
+#pragma unroll
+                for (int r = 0; r < R; ++r) ys[r] = fma(h0, k1[r], y[r]);
+                LASSIM_RHS(ys, k2);
+                double d2 = 0.0;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const double sc = fma(rtol, fabs(y[r]), atol);
+                    d2 = fmax(d2, fabs(k2[r] - k1[r]) / sc);
+                }
+                d2 = group_max<G>(d2, gmask) / h0;
+                const double dm = fmax(d1, d2);
+                const double h1 = (dm <= 1e-15) ? fmax(1e-6, h0 * 1e-3)
+                                                : pow(0.01 / dm, 0.2);
+                h = fmin(100.0 * h0, h1);
+                active = true;
+                if (nt < 2 || !(tend > t)) ti = nt;   // empty span: end = start
+            }
+        }
+        if (!__any_sync(0xffffffffu, active)) break;
+
+        if (active && ti < nt) {
+            // ---------------------------------------------------- one attempt
+            double hs = h;
+            bool hit = false;
+            if (t + 1.01 * hs >= tend) { hs = tend - t; hit = true; }
+            double part[R];   // terms of the next stage that are already known
+#pragma unroll
+            for (int r = 0; r < R; ++r) ys[r] = fma(hs * DP_A21, k1[r], y[r]);
+            LASSIM_RHS(ys, k2);
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                ys[r] = fma(hs, fma(DP_A32, k2[r], DP_A31 * k1[r]), y[r]);
+#pragma unroll
+            for (int r = 0; r < R; ++r) part[r] = fma(DP_A42, k2[r], DP_A41 * k1[r]);
+            LASSIM_RHS(ys, k3);
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                ys[r] = fma(hs, fma(DP_A43, k3[r], part[r]), y[r]);
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                part[r] = fma(DP_A53, k3[r], fma(DP_A52, k2[r], DP_A51 * k1[r]));
+            LASSIM_RHS(ys, k4);
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                ys[r] = fma(hs, fma(DP_A54, k4[r], part[r]), y[r]);
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                part[r] = fma(DP_A64, k4[r],
+                              fma(DP_A63, k3[r], fma(DP_A62, k2[r], DP_A61 * k1[r])));
+            LASSIM_RHS(ys, k5);
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                ys[r] = fma(hs, fma(DP_A65, k5[r], part[r]), y[r]);
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                part[r] = fma(DP_B5, k5[r],
+                              fma(DP_B4, k4[r], fma(DP_B3, k3[r], DP_B1 * k1[r])));
+            LASSIM_RHS(ys, k6);
+            double epart[R], isc[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                yn[r] = fma(hs, fma(DP_B6, k6[r], part[r]), y[r]);
+                epart[r] = fma(DP_E6, k6[r],
+                               fma(DP_E5, k5[r],
+                                   fma(DP_E4, k4[r], fma(DP_E3, k3[r], DP_E1 * k1[r]))));
+            }
+            // the error weight only needs y and yn: off the critical path
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                isc[r] = 1.0 / fma(rtol, fmax(fabs(y[r]), fabs(yn[r])), atol);
+            LASSIM_RHS(yn, k7);
+            double q = 0.0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const double e = hs * fma(DP_E7, k7[r], epart[r]);
+                double qr = fabs(e) * isc[r];
+                if (!(qr <= 1.79e308)) qr = CUDART_INF;   // NaN or inf
+                q = fmax(q, qr);
+            }
+            const float qf = group_max_nonneg(q, gmask);
+
+            bool finished = false;
+            const float qc = fminf(fmaxf(qf, 1e-30f), 3.0e38f);
+            const float fac0 = 0.9f * exp2f(-0.2f * __log2f(qc));
+            if (qf <= 1.0f) {
+                ++nacc;
+                t = hit ? tend : t + hs;
+#pragma unroll
+                for (int r = 0; r < R; ++r) { y[r] = yn[r]; k1[r] = k7[r]; }
+                float fac = fminf(10.0f, fmaxf(0.2f, fac0));
+                if (rejected) fac = fminf(fac, 1.0f);
+                rejected = false;
+                const double hnew = hs * (double)fac;
+                h = hit ? fmax(hnew, h) : hnew;
+                if (hit) {
+                    if (k == 0) {
+                        double *Yc = B.Y + ((size_t)c * P.T + ti) * n;
+#pragma unroll
+                        for (int r = 0; r < R; ++r)
+                            if (gene_ok[r]) Yc[lg * R + r] = y[r];
+                    }
+                    ++ti;
+                    if (ti < nt) tend = tl[ti];
+                }
+            } else {
+                ++nrej;
+                rejected = true;
+                h = hs * (double)fmaxf(0.2f, fminf(fac0, 1.0f));
+                if (!(fabs(h) > 1e-290) || t + h == t) { st |= 2; finished = true; }
+            }
+            if (!finished && ti < nt && nacc + nrej >= P.max_steps) {
+                st |= 1;
+                finished = true;
+            }
+            if (finished) {
+                // failed trajectory: poison what it would have produced
+#pragma unroll
+                for (int r = 0; r < R; ++r) y[r] = CUDART_NAN;
+                if (k == 0) {
+                    for (int s = ti; s < nt; ++s) {
+                        double *Yc = B.Y + ((size_t)c * P.T + s) * n;
+#pragma unroll
+                        for (int r = 0; r < R; ++r)
+                            if (gene_ok[r]) Yc[lg * R + r] = CUDART_NAN;
+                    }
+                }
+                ti = nt;
+            }
+        }
+
+        if (active && ti >= nt) {
+            // ------------------------------------------------------ epilogue
+            if (k == 0) {
+                const double *Yc = B.Y + (size_t)c * P.T * n;
+                double part = 0.0;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    if (gene_ok[r]) {
+                        const int g = lg * R + r;
+                        double m = -CUDART_INF;
+                        bool isnan_ = false;
+                        for (int s = 0; s < P.T; ++s) {
+                            const double v = Yc[s * n + g];
+                            isnan_ |= (v != v);
+                            m = fmax(m, v);
+                        }
+                        if (isnan_) m = CUDART_NAN;   // numpy.amax propagates NaN
+                        const double s2 = P.sigma2[g];
+                        for (int s = 0; s < P.T; ++s) {
+                            const double d = P.data[s * n + g] - Yc[s * n + g] / m;
+                            part += d * d / s2;
+                        }
+                    }
+                }
+                part = group_sum<G>(part, gmask);
+                if (lg == 0) B.cost_main[c] = part;
+            } else {
+                double *Ec = B.E + ((size_t)c * P.K + k) * n;
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    if (gene_ok[r]) Ec[lg * R + r] = y[r];
+            }
+            if (lg == 0) {
+                B.traj_steps[(size_t)c * P.K + k] = nacc + nrej;
+                atomicAdd(&B.counters[(size_t)c * 3 + 0], (unsigned long long)nacc);
+                atomicAdd(&B.counters[(size_t)c * 3 + 1], (unsigned long long)nrej);
+                atomicAdd(&B.counters[(size_t)c * 3 + 2],
+                          (unsigned long long)(6u * (nacc + nrej) + 2u));
+                if (st) atomicOr(&B.status[c], st);
+            }
+            active = false;
+            if (B.mode == 0) {
+                __threadfence();
+                __syncwarp(gmask);
+                int old = 0;
+                if (lg == 0) old = atomicAdd(&B.done[c], 1);
+                old = __shfl_sync(gmask, old, 0, G);
+                if (old == Kc - 1) {
+                    // last trajectory of candidate c: knock-down cost + total
+                    __threadfence();
+                    double pc = 0.0;
+                    if (P.K > 1) {
+                        const int np2 = n + 2;
+                        double rmax = 0.0, pp = 0.0;
+                        for (int i = 0; i < n; ++i) {
+                            const double *Es = B.E + ((size_t)c * P.K + 1 + P.U + i) * n;
+                            const double *Ecn = B.E + ((size_t)c * P.K + P.knock_ctrl[i]) * n;
+#pragma unroll
+                            for (int r = 0; r < R; ++r) {
+                                if (gene_ok[r]) {
+                                    const int g = lg * R + r;
+                                    double rr = __ldcg(Es + g) / __ldcg(Ecn + g) - 1.0;
+                                    if (rr > 2.0) rr = 2.0;
+                                    rmax = fmax(rmax, fabs(rr));
+                                    const double p = P.pert[(size_t)i * np2 + g];
+                                    pp = fma(p, p, pp);
+                                }
+                            }
+                        }
+                        rmax = group_max<G>(rmax, gmask);
+                        pp = group_sum<G>(pp, gmask);
+                        double rp = 0.0, rr2 = 0.0;
+                        const double inv = (rmax > 0.0) ? 1.0 / rmax : 0.0;
+                        for (int i = 0; i < n; ++i) {
+                            const double *Es = B.E + ((size_t)c * P.K + 1 + P.U + i) * n;
+                            const double *Ecn = B.E + ((size_t)c * P.K + P.knock_ctrl[i]) * n;
+#pragma unroll
+                            for (int r = 0; r < R; ++r) {
+                                if (gene_ok[r]) {
+                                    const int g = lg * R + r;
+                                    double rr = __ldcg(Es + g) / __ldcg(Ecn + g) - 1.0;
+                                    if (rr > 2.0) rr = 2.0;
+                                    rr *= inv;
+                                    const double p = P.pert[(size_t)i * np2 + g];
+                                    rp = fma(rr, p, rp);
+                                    rr2 = fma(rr, rr, rr2);
+                                }
+                            }
+                        }
+                        rp = group_sum<G>(rp, gmask);
+                        rr2 = group_sum<G>(rr2, gmask);
+                        pc = (rmax > 0.0) ? pp - rp * rp / rr2 : pp;
+                    }
+                    if (lg == 0) {
+                        const double cm = __ldcg(B.cost_main + c);
+                        B.pert_cost[c] = pc;
+                        B.cost[c] = (P.K > 1) ? fma(P.pert_factor, pc, cm) : cm;
+                    }
+                }
+            }
+        }
+    }
+#undef LASSIM_RHS
+}
+
+// Register-resident DFMA throughput probe (roofline denominator).
+__global__ void __launch_bounds__(256) fp64_probe_kernel(double *out, int iters,
+                                                         double seed) {
+    double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3;
+    double a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const double m = 0.999999, b = 1e-9;
+    for (int i = 0; i < iters; ++i) {
+        a0 = fma(a0, m, b); a1 = fma(a1, m, b); a2 = fma(a2, m, b); a3 = fma(a3, m, b);
+        a4 = fma(a4, m, b); a5 = fma(a5, m, b); a6 = fma(a6, m, b); a7 = fma(a7, m, b);
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] =
+        a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+}  // namespace lassim

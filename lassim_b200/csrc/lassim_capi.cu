@@ -1,0 +1,519 @@
+// Host side of liblassim_b200.so: the C ABI declared in include/lassim_b200.h.
+// Owns the device copies of the problem constants, the scratch buffers and the
+// launch logic for the kernels in grn_kernels.cuh.  There is no CPU fallback:
+// every evaluation entry point launches a CUDA kernel or fails.
+#include "../../include/lassim_b200.h"
+#include "grn_kernels.cuh"
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace lassim;
+
+namespace {
+
+std::string g_create_error;
+
+template <typename T>
+struct DevBuf {
+    T *p = nullptr;
+    size_t cap = 0;   // elements
+    cudaError_t reserve(size_t count) {
+        if (count <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc(&p, count * sizeof(T));
+        if (e == cudaSuccess) cap = count;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+}  // namespace
+
+struct lassim_handle {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    std::string err;
+    long long launches = 0;
+
+    // problem (host copies)
+    bool has_problem = false;
+    int n = 0, T = 0, K = 1, U = 0, nnz = 0, dim = 0;
+    std::vector<double> pert_h;
+    double pert_factor = 0.0;
+    double rtol = 1.49012e-8, atol = 1.49012e-8;
+    long long max_steps = 20000000;
+
+    // problem (device)
+    DevBuf<double> d_times, d_y0, d_data, d_sigma2, d_pert, d_traj_tt;
+    DevBuf<int> d_kidx, d_traj_prefix, d_knock_ctrl;
+
+    // scratch
+    DevBuf<double> d_X, d_cost, d_cost_main, d_pert_cost, d_Y, d_E, d_probe;
+    DevBuf<unsigned char> d_zero;   // work counter | done | status | counters
+    DevBuf<unsigned int> d_steps;
+    int last_N = 0;
+    bool last_had_E = false;
+};
+
+namespace {
+
+int fail(lassim_handle *h, int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (h) h->err = buf; else g_create_error = buf;
+    return code;
+}
+
+#define CU(call)                                                               \
+    do {                                                                       \
+        cudaError_t e_ = (call);                                               \
+        if (e_ != cudaSuccess)                                                 \
+            return fail(h, LASSIM_E_CUDA, "%s failed: %s", #call,              \
+                        cudaGetErrorString(e_));                               \
+    } while (0)
+
+template <typename T>
+int upload(lassim_handle *h, DevBuf<T> &buf, const T *src, size_t count) {
+    CU(buf.reserve(count ? count : 1));
+    if (count)
+        CU(cudaMemcpyAsync(buf.p, src, count * sizeof(T), cudaMemcpyHostToDevice,
+                           h->stream));
+    return LASSIM_OK;
+}
+
+int upload_mask(lassim_handle *h, const unsigned char *mask) {
+    const int n = h->n;
+    std::vector<int> kidx((size_t)n * n);
+    int cnt = 0;
+    for (int i = 0; i < n * n; ++i) kidx[i] = mask[i] ? cnt++ : -1;
+    h->nnz = cnt;
+    h->dim = 2 * n + cnt;
+    int rc = upload(h, h->d_kidx, kidx.data(), kidx.size());
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(h->stream));   // kidx is a local
+    return LASSIM_OK;
+}
+
+struct ZeroLayout {
+    size_t off_done, off_status, off_counters, bytes;
+};
+
+ZeroLayout zero_layout(int N) {
+    ZeroLayout z;
+    z.off_done = 16;
+    z.off_status = z.off_done + sizeof(int) * (size_t)N;
+    z.off_counters = (z.off_status + sizeof(int) * (size_t)N + 15) & ~(size_t)15;
+    z.bytes = z.off_counters + sizeof(unsigned long long) * 3 * (size_t)N;
+    return z;
+}
+
+typedef void (*kernel_fn)(const DevProblem, const DevBatch);
+
+struct KernelChoice {
+    kernel_fn fn;
+    int G, R;
+};
+
+template <int G, int R, bool FAST>
+kernel_fn pick_columns(int n) {
+    constexpr int NP = G * R;
+    const int nc = (n + 3) & ~3;
+    if (nc <= 4 && 4 <= NP) return grn_cost_kernel<G, R, 4 <= NP ? 4 : NP, FAST>;
+    if (nc <= 8 && 8 <= NP) return grn_cost_kernel<G, R, 8 <= NP ? 8 : NP, FAST>;
+    if (nc <= 12 && 12 <= NP) return grn_cost_kernel<G, R, 12 <= NP ? 12 : NP, FAST>;
+    if (nc <= 16 && 16 <= NP) return grn_cost_kernel<G, R, 16 <= NP ? 16 : NP, FAST>;
+    if (nc <= 24 && 24 <= NP) return grn_cost_kernel<G, R, 24 <= NP ? 24 : NP, FAST>;
+    return grn_cost_kernel<G, R, NP, FAST>;
+}
+
+// Which lane-group shape serves a state size.  LASSIM_GROUP=G overrides the
+// choice between shapes that both fit and LASSIM_EXACT_MATH=1 selects libm
+// exp + IEEE division instead of the exp2/Newton logistic (diagnostics).
+bool choose_kernel(int n, KernelChoice *out) {
+    const char *env = getenv("LASSIM_GROUP");
+    const int want = env ? atoi(env) : 0;
+    const char *ex = getenv("LASSIM_EXACT_MATH");
+    const bool fast = !(ex && atoi(ex) != 0);
+    if (n <= 12 && want == 4) {
+        *out = {fast ? pick_columns<4, 3, true>(n) : pick_columns<4, 3, false>(n), 4, 3};
+        return true;
+    }
+    if (n <= 16 && want == 8) {
+        *out = {fast ? pick_columns<8, 2, true>(n) : pick_columns<8, 2, false>(n), 8, 2};
+        return true;
+    }
+    if (n <= 16) {
+        *out = {fast ? pick_columns<16, 1, true>(n) : pick_columns<16, 1, false>(n), 16, 1};
+        return true;
+    }
+    if (n <= 32) {
+        *out = {fast ? pick_columns<32, 1, true>(n) : pick_columns<32, 1, false>(n), 32, 1};
+        return true;
+    }
+    return false;
+}
+
+int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
+                cudaStream_t s) {
+    KernelChoice kc;
+    if (!choose_kernel(h->n, &kc))
+        return fail(h, LASSIM_E_UNSUPPORTED,
+                    "state size n=%d is outside the kernels built (n <= 32)", h->n);
+    const int K = h->K, n = h->n;
+    const ZeroLayout z = zero_layout(N);
+    CU(h->d_zero.reserve(z.bytes));
+    CU(h->d_cost.reserve(N));
+    CU(h->d_cost_main.reserve(N));
+    CU(h->d_pert_cost.reserve(N));
+    CU(h->d_steps.reserve((size_t)N * K));
+    if (!dY) {
+        CU(h->d_Y.reserve((size_t)N * h->T * n));
+        dY = h->d_Y.p;
+    }
+    if (K > 1 && mode == 0) CU(h->d_E.reserve((size_t)N * K * n));
+    CU(cudaMemsetAsync(h->d_zero.p, 0, z.bytes, s));
+    if (mode == 0) CU(cudaMemsetAsync(h->d_steps.p, 0, sizeof(unsigned) * (size_t)N * K, s));
+
+    DevProblem P;
+    P.n = n; P.T = h->T; P.K = K; P.U = h->U; P.dim = h->dim; P.nnz = h->nnz;
+    P.times = h->d_times.p; P.y0 = h->d_y0.p; P.data = h->d_data.p;
+    P.sigma2 = h->d_sigma2.p; P.kidx = h->d_kidx.p;
+    P.pert = (K > 1) ? h->d_pert.p : nullptr;
+    P.traj_prefix = h->d_traj_prefix.p; P.traj_tt = h->d_traj_tt.p;
+    P.knock_ctrl = h->d_knock_ctrl.p;
+    P.pert_factor = h->pert_factor; P.rtol = h->rtol; P.atol = h->atol;
+    P.max_steps = (unsigned int)(h->max_steps > 4000000000LL ? 4000000000LL : h->max_steps);
+
+    DevBatch B;
+    B.N = N; B.mode = mode; B.X = dX;
+    B.cost = h->d_cost.p; B.cost_main = h->d_cost_main.p; B.pert_cost = h->d_pert_cost.p;
+    B.work_counter = reinterpret_cast<unsigned int *>(h->d_zero.p);
+    B.done = reinterpret_cast<int *>(h->d_zero.p + z.off_done);
+    B.status = reinterpret_cast<int *>(h->d_zero.p + z.off_status);
+    B.counters = reinterpret_cast<unsigned long long *>(h->d_zero.p + z.off_counters);
+    B.Y = dY; B.E = h->d_E.p; B.traj_steps = h->d_steps.p; B.order = nullptr;
+
+    const int groups_per_cta = kThreads / kc.G;
+    const size_t smem = (64 + (size_t)groups_per_cta * 2 * (kc.G * kc.R + 2)) * sizeof(double);
+    int per_sm = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kc.fn, kThreads, smem));
+    if (per_sm < 1) per_sm = 1;
+    const long long work = (long long)N * (mode == 0 ? K : 1);
+    long long blocks = (work + groups_per_cta - 1) / groups_per_cta;
+    const long long resident = (long long)h->sm_count * per_sm;
+    if (blocks > resident) blocks = resident;
+    if (blocks < 1) blocks = 1;
+
+    CU(cudaEventRecord(h->ev0, s));
+    kc.fn<<<(unsigned)blocks, kThreads, smem, s>>>(P, B);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(h->ev1, s));
+    h->timed = true;
+    h->launches += 1;
+    h->last_N = N;
+    h->last_had_E = (K > 1 && mode == 0);
+    return LASSIM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *lassim_version(void) { return "0.1.0"; }
+
+const char *lassim_last_error(const lassim_handle *h) {
+    return h ? h->err.c_str() : g_create_error.c_str();
+}
+
+int lassim_create(int device, lassim_handle **out) {
+    lassim_handle *h = nullptr;
+    if (!out) return fail(nullptr, LASSIM_E_INVALID, "out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, LASSIM_E_CUDA, "no CUDA device: %s",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= count)
+        return fail(nullptr, LASSIM_E_INVALID, "device %d out of range [0,%d)", device, count);
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess)
+        return fail(nullptr, LASSIM_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess)
+        return fail(nullptr, LASSIM_E_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e));
+    if (prop.major != 10)
+        return fail(nullptr, LASSIM_E_UNSUPPORTED,
+                    "device %d is sm_%d%d; this library is built for sm_100a only",
+                    device, prop.major, prop.minor);
+    h = new lassim_handle();
+    h->device = device;
+    h->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess) {
+        delete h;
+        return fail(nullptr, LASSIM_E_CUDA, "stream/event creation failed");
+    }
+    double tab[64];
+    for (int j = 0; j < 64; ++j) tab[j] = exp2((double)j / 64.0);
+    if (cudaMemcpyToSymbol(c_exp2_table, tab, sizeof(tab)) != cudaSuccess) {
+        lassim_destroy(h);
+        return fail(nullptr, LASSIM_E_CUDA, "upload of the exp2 table failed");
+    }
+    *out = h;
+    return LASSIM_OK;
+}
+
+int lassim_destroy(lassim_handle *h) {
+    if (!h) return LASSIM_OK;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    h->d_times.release(); h->d_y0.release(); h->d_data.release(); h->d_sigma2.release();
+    h->d_pert.release(); h->d_traj_tt.release(); h->d_kidx.release();
+    h->d_traj_prefix.release(); h->d_knock_ctrl.release();
+    h->d_X.release(); h->d_cost.release(); h->d_cost_main.release();
+    h->d_pert_cost.release(); h->d_Y.release(); h->d_E.release(); h->d_probe.release();
+    h->d_zero.release(); h->d_steps.release();
+    cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
+    cudaStreamDestroy(h->stream);
+    delete h;
+    return LASSIM_OK;
+}
+
+int lassim_set_problem(lassim_handle *h, int n, int T, const double *times,
+                       const double *y0, const double *data, const double *sigma,
+                       const unsigned char *mask, const double *pert,
+                       double pert_factor) {
+    if (!h) return LASSIM_E_INVALID;
+    if (n < 1 || T < 1 || !times || !y0 || !data || !sigma || !mask)
+        return fail(h, LASSIM_E_INVALID, "set_problem: n=%d T=%d or a NULL array", n, T);
+    KernelChoice kc;
+    if (!choose_kernel(n, &kc))
+        return fail(h, LASSIM_E_UNSUPPORTED,
+                    "state size n=%d is outside the kernels built (n <= 32)", n);
+    CU(cudaSetDevice(h->device));
+    h->has_problem = false;
+    h->n = n; h->T = T; h->pert_factor = pert_factor;
+    std::vector<double> sigma2(n);
+    for (int i = 0; i < n; ++i) sigma2[i] = sigma[i] * sigma[i];
+    int rc;
+    if ((rc = upload(h, h->d_times, times, (size_t)T))) return rc;
+    if ((rc = upload(h, h->d_y0, y0, (size_t)n))) return rc;
+    if ((rc = upload(h, h->d_data, data, (size_t)T * n))) return rc;
+    if ((rc = upload(h, h->d_sigma2, sigma2.data(), (size_t)n))) return rc;
+
+    // trajectory table: 0 = time series; 1..U = controls in order of first
+    // appearance of their (t_start, t_end) pair, solved with the lambdas as
+    // scaled by the rows before that appearance; 1+U+i = row i knocked
+    // (perturbation_functions.pyx:64-85).
+    std::vector<int> prefix(1, 0), knock_ctrl;
+    std::vector<double> tt(2, 0.0);
+    h->U = 0; h->K = 1;
+    h->pert_h.clear();
+    if (pert) {
+        const int np2 = n + 2;
+        h->pert_h.assign(pert, pert + (size_t)n * np2);
+        std::vector<std::pair<double, double>> pairs;
+        std::vector<int> first_row;
+        knock_ctrl.resize(n);
+        for (int i = 0; i < n; ++i) {
+            const std::pair<double, double> p(pert[(size_t)i * np2 + n],
+                                              pert[(size_t)i * np2 + n + 1]);
+            int u = -1;
+            for (size_t q = 0; q < pairs.size(); ++q)
+                if (pairs[q] == p) { u = (int)q; break; }
+            if (u < 0) { u = (int)pairs.size(); pairs.push_back(p); first_row.push_back(i); }
+            knock_ctrl[i] = 1 + u;
+        }
+        h->U = (int)pairs.size();
+        h->K = 1 + h->U + n;
+        prefix.resize(h->K); tt.resize(2 * (size_t)h->K);
+        for (int u = 0; u < h->U; ++u) {
+            prefix[1 + u] = first_row[u];
+            tt[2 * (1 + u)] = pairs[u].first; tt[2 * (1 + u) + 1] = pairs[u].second;
+        }
+        for (int i = 0; i < n; ++i) {
+            const int k = 1 + h->U + i;
+            prefix[k] = i + 1;
+            tt[2 * k] = pert[(size_t)i * np2 + n]; tt[2 * k + 1] = pert[(size_t)i * np2 + n + 1];
+        }
+        if ((rc = upload(h, h->d_pert, pert, (size_t)n * np2))) return rc;
+        if ((rc = upload(h, h->d_knock_ctrl, knock_ctrl.data(), (size_t)n))) return rc;
+    }
+    if ((rc = upload(h, h->d_traj_prefix, prefix.data(), prefix.size()))) return rc;
+    if ((rc = upload(h, h->d_traj_tt, tt.data(), tt.size()))) return rc;
+    if ((rc = upload_mask(h, mask))) return rc;   // synchronises: locals are done
+    h->has_problem = true;
+    return LASSIM_OK;
+}
+
+int lassim_set_mask(lassim_handle *h, const unsigned char *mask) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->has_problem) return fail(h, LASSIM_E_STATE, "set_mask before set_problem");
+    if (!mask) return fail(h, LASSIM_E_INVALID, "mask is NULL");
+    CU(cudaSetDevice(h->device));
+    return upload_mask(h, mask);
+}
+
+int lassim_set_tolerances(lassim_handle *h, double rtol, double atol, long long max_steps) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!(rtol > 0.0) || !(atol >= 0.0) || max_steps < 1)
+        return fail(h, LASSIM_E_INVALID, "tolerances must be positive (rtol=%g atol=%g max_steps=%lld)",
+                    rtol, atol, max_steps);
+    h->rtol = rtol; h->atol = atol; h->max_steps = max_steps;
+    return LASSIM_OK;
+}
+
+int lassim_dim(const lassim_handle *h) { return (h && h->has_problem) ? h->dim : -1; }
+
+int lassim_trajectories_per_candidate(const lassim_handle *h) {
+    return (h && h->has_problem) ? h->K : -1;
+}
+
+int lassim_eval_device(lassim_handle *h, int N, const double *dX, double *dcost,
+                       double *dcost_main, double *dpert_cost, int *dstatus,
+                       unsigned long long *dcounters, void *stream) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->has_problem) return fail(h, LASSIM_E_STATE, "eval before set_problem");
+    if (N < 0 || (N > 0 && (!dX || !dcost)))
+        return fail(h, LASSIM_E_INVALID, "eval: N=%d, X or cost is NULL", N);
+    if (N == 0) return LASSIM_OK;
+    CU(cudaSetDevice(h->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+    int rc = launch_eval(h, N, 0, dX, nullptr, s);
+    if (rc) return rc;
+    const ZeroLayout z = zero_layout(N);
+    const size_t nb = sizeof(double) * (size_t)N;
+    CU(cudaMemcpyAsync(dcost, h->d_cost.p, nb, cudaMemcpyDeviceToDevice, s));
+    if (dcost_main) CU(cudaMemcpyAsync(dcost_main, h->d_cost_main.p, nb, cudaMemcpyDeviceToDevice, s));
+    if (dpert_cost) CU(cudaMemcpyAsync(dpert_cost, h->d_pert_cost.p, nb, cudaMemcpyDeviceToDevice, s));
+    if (dstatus) CU(cudaMemcpyAsync(dstatus, h->d_zero.p + z.off_status, sizeof(int) * (size_t)N,
+                                    cudaMemcpyDeviceToDevice, s));
+    if (dcounters) CU(cudaMemcpyAsync(dcounters, h->d_zero.p + z.off_counters,
+                                      sizeof(unsigned long long) * 3 * (size_t)N,
+                                      cudaMemcpyDeviceToDevice, s));
+    return LASSIM_OK;
+}
+
+int lassim_eval(lassim_handle *h, int N, const double *X, double *cost,
+                double *cost_main, double *pert_cost, int *status,
+                unsigned long long *counters) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->has_problem) return fail(h, LASSIM_E_STATE, "eval before set_problem");
+    if (N < 0 || (N > 0 && (!X || !cost)))
+        return fail(h, LASSIM_E_INVALID, "eval: N=%d, X or cost is NULL", N);
+    if (N == 0) return LASSIM_OK;
+    CU(cudaSetDevice(h->device));
+    cudaStream_t s = h->stream;
+    CU(h->d_X.reserve((size_t)N * h->dim));
+    CU(cudaMemcpyAsync(h->d_X.p, X, sizeof(double) * (size_t)N * h->dim,
+                       cudaMemcpyHostToDevice, s));
+    int rc = launch_eval(h, N, 0, h->d_X.p, nullptr, s);
+    if (rc) return rc;
+    const ZeroLayout z = zero_layout(N);
+    const size_t nb = sizeof(double) * (size_t)N;
+    CU(cudaMemcpyAsync(cost, h->d_cost.p, nb, cudaMemcpyDeviceToHost, s));
+    if (cost_main) CU(cudaMemcpyAsync(cost_main, h->d_cost_main.p, nb, cudaMemcpyDeviceToHost, s));
+    if (pert_cost) CU(cudaMemcpyAsync(pert_cost, h->d_pert_cost.p, nb, cudaMemcpyDeviceToHost, s));
+    if (status) CU(cudaMemcpyAsync(status, h->d_zero.p + z.off_status, sizeof(int) * (size_t)N,
+                                   cudaMemcpyDeviceToHost, s));
+    if (counters) CU(cudaMemcpyAsync(counters, h->d_zero.p + z.off_counters,
+                                     sizeof(unsigned long long) * 3 * (size_t)N,
+                                     cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    return LASSIM_OK;
+}
+
+int lassim_trajectories(lassim_handle *h, int N, const double *X, double *Y, int *status) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->has_problem) return fail(h, LASSIM_E_STATE, "trajectories before set_problem");
+    if (N < 0 || (N > 0 && (!X || !Y)))
+        return fail(h, LASSIM_E_INVALID, "trajectories: N=%d, X or Y is NULL", N);
+    if (N == 0) return LASSIM_OK;
+    CU(cudaSetDevice(h->device));
+    cudaStream_t s = h->stream;
+    CU(h->d_X.reserve((size_t)N * h->dim));
+    CU(cudaMemcpyAsync(h->d_X.p, X, sizeof(double) * (size_t)N * h->dim,
+                       cudaMemcpyHostToDevice, s));
+    int rc = launch_eval(h, N, 1, h->d_X.p, nullptr, s);
+    if (rc) return rc;
+    const ZeroLayout z = zero_layout(N);
+    CU(cudaMemcpyAsync(Y, h->d_Y.p, sizeof(double) * (size_t)N * h->T * h->n,
+                       cudaMemcpyDeviceToHost, s));
+    if (status) CU(cudaMemcpyAsync(status, h->d_zero.p + z.off_status, sizeof(int) * (size_t)N,
+                                   cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    return LASSIM_OK;
+}
+
+int lassim_last_end_states(lassim_handle *h, int N, double *E) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->last_had_E || N != h->last_N || !E)
+        return fail(h, LASSIM_E_STATE, "no knock-down end states for N=%d (last N=%d)", N, h->last_N);
+    CU(cudaSetDevice(h->device));
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(E, h->d_E.p, sizeof(double) * (size_t)N * h->K * h->n, cudaMemcpyDeviceToHost));
+    return LASSIM_OK;
+}
+
+int lassim_last_traj_steps(lassim_handle *h, int N, unsigned int *steps) {
+    if (!h) return LASSIM_E_INVALID;
+    if (N != h->last_N || !steps)
+        return fail(h, LASSIM_E_STATE, "no step counts for N=%d (last N=%d)", N, h->last_N);
+    CU(cudaSetDevice(h->device));
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(steps, h->d_steps.p, sizeof(unsigned) * (size_t)N * h->K, cudaMemcpyDeviceToHost));
+    return LASSIM_OK;
+}
+
+long long lassim_launch_count(const lassim_handle *h) { return h ? h->launches : -1; }
+
+int lassim_last_kernel_ms(lassim_handle *h, float *ms) {
+    if (!h || !ms) return LASSIM_E_INVALID;
+    if (!h->timed) return fail(h, LASSIM_E_STATE, "no kernel has been launched yet");
+    CU(cudaSetDevice(h->device));
+    CU(cudaEventSynchronize(h->ev1));
+    CU(cudaEventElapsedTime(ms, h->ev0, h->ev1));
+    return LASSIM_OK;
+}
+
+int lassim_fp64_peak_probe(lassim_handle *h, int iters, double *tflops) {
+    if (!h || !tflops || iters < 1) return LASSIM_E_INVALID;
+    CU(cudaSetDevice(h->device));
+    const int blocks = h->sm_count * 8, threads = 256;
+    CU(h->d_probe.reserve((size_t)blocks * threads));
+    cudaStream_t s = h->stream;
+    fp64_probe_kernel<<<blocks, threads, 0, s>>>(h->d_probe.p, iters / 8 + 1, 0.5);  // warm-up
+    CU(cudaGetLastError());
+    float best = 1e30f;
+    for (int rep = 0; rep < 3; ++rep) {
+        CU(cudaEventRecord(h->ev0, s));
+        fp64_probe_kernel<<<blocks, threads, 0, s>>>(h->d_probe.p, iters, 0.5);
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(h->ev1, s));
+        CU(cudaEventSynchronize(h->ev1));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+        if (ms < best) best = ms;
+        h->launches += 1;
+    }
+    h->timed = false;
+    const double flops = 2.0 * 8.0 * (double)iters * (double)blocks * threads;
+    *tflops = flops / (best * 1e-3) / 1e12;
+    return LASSIM_OK;
+}
+
+}  // extern "C"
