@@ -101,8 +101,10 @@ int lassim_eval(lassim_handle *h, int N, const double *X, double *cost,
                 unsigned long long *counters);
 
 /* Same, with X and every non-NULL output in DEVICE memory, enqueued on
- * `stream` (a cudaStream_t passed as void*; NULL = the handle's own stream).
- * Returns after the launch; synchronise the stream before reading. */
+ * `stream` (a cudaStream_t passed as void*).  NULL selects the handle's own
+ * non-blocking stream, NOT the legacy default stream: to run on the default
+ * stream pass cudaStreamLegacy or cudaStreamPerThread explicitly.  Returns
+ * after the launch; synchronise the stream before reading. */
 int lassim_eval_device(lassim_handle *h, int N, const double *dX, double *dcost,
                        double *dcost_main, double *dpert_cost, int *dstatus,
                        unsigned long long *dcounters, void *stream);
@@ -124,7 +126,8 @@ int lassim_trajectories(lassim_handle *h, int N, const double *X, double *Y,
  */
 int lassim_last_end_states(lassim_handle *h, int N, double *E);
 
-/* Step attempts per trajectory of the LAST evaluation: steps[N*K]. */
+/* Step attempts per trajectory of the LAST evaluation: steps[N*K] (after
+ * lassim_trajectories only slot 0 of each candidate is non-zero). */
 int lassim_last_traj_steps(lassim_handle *h, int N, unsigned int *steps);
 
 /* Number of kernels this handle has launched so far. */

@@ -309,7 +309,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                                                 : pow(0.01 / dm, 0.2);
                 h = fmin(100.0 * h0, h1);
                 active = true;
-                if (nt < 2 || !(tend > t)) ti = nt;   // empty span: end = start
+                if (nt < 2) ti = nt;   // a single sample time: nothing to integrate
             }
         }
         if (!__any_sync(0xffffffffu, active)) break;

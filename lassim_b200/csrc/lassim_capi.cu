@@ -184,7 +184,7 @@ int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
     }
     if (K > 1 && mode == 0) CU(h->d_E.reserve((size_t)N * K * n));
     CU(cudaMemsetAsync(h->d_zero.p, 0, z.bytes, s));
-    if (mode == 0) CU(cudaMemsetAsync(h->d_steps.p, 0, sizeof(unsigned) * (size_t)N * K, s));
+    CU(cudaMemsetAsync(h->d_steps.p, 0, sizeof(unsigned) * (size_t)N * K, s));
 
     DevProblem P;
     P.n = n; P.T = h->T; P.K = K; P.U = h->U; P.dim = h->dim; P.nnz = h->nnz;
@@ -304,6 +304,16 @@ int lassim_set_problem(lassim_handle *h, int n, int T, const double *times,
     if (!choose_kernel(n, &kc))
         return fail(h, LASSIM_E_UNSUPPORTED,
                     "state size n=%d is outside the kernels built (n <= 32)", n);
+    for (int i = 1; i < T; ++i)
+        if (!(times[i] >= times[i - 1]))
+            return fail(h, LASSIM_E_UNSUPPORTED,
+                        "sample times must be non-decreasing (times[%d]=%g < times[%d]=%g)",
+                        i, times[i], i - 1, times[i - 1]);
+    if (pert)
+        for (int i = 0; i < n; ++i)
+            if (!(pert[(size_t)i * (n + 2) + n + 1] >= pert[(size_t)i * (n + 2) + n]))
+                return fail(h, LASSIM_E_UNSUPPORTED,
+                            "perturbation row %d has t_end < t_start", i);
     CU(cudaSetDevice(h->device));
     h->has_problem = false;
     h->n = n; h->T = T; h->pert_factor = pert_factor;

@@ -1,0 +1,135 @@
+"""Batched DE / island / archipelago driver on CPU problems, including the
+two-process (gloo) island sharding."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from lassim_b200.pygmo import algorithm, archipelago, island, topology
+from lassim_b200.pygmo.problem import base
+
+from conftest import REPO
+
+
+class Sphere(base):
+    calls = 0
+    batches = 0
+
+    def __init__(self, dim=6):
+        super().__init__(dim)
+        self.set_bounds(-5.0, 5.0)
+
+    def _objfun_impl(self, x):
+        return (float(np.sum((np.asarray(x) - 1.0) ** 2)),)
+
+    def objfun_batch(self, X):
+        Sphere.batches += 1
+        Sphere.calls += len(X)
+        return np.sum((np.asarray(X) - 1.0) ** 2, axis=1)
+
+
+@pytest.mark.parametrize("variant", range(1, 11))
+def test_de_variants_improve(variant):
+    prob = Sphere(6)
+    algo = algorithm.de(gen=60, f=0.7, cr=0.9, variant=variant)
+    isl = island(algo, prob, 24, seed=variant)
+    isl.population.evaluate()
+    start = isl.population.champion.f[0]
+    isl.evolve(1)
+    end = isl.population.champion.f[0]
+    assert end < 0.05 * start
+    X = isl.population.X
+    assert (X >= -5).all() and (X <= 5).all()
+
+
+def test_de_rejects_small_population_and_bad_params():
+    with pytest.raises(ValueError):
+        algorithm.de(variant=11)
+    with pytest.raises(ValueError):
+        algorithm.de(f=1.5)
+    isl = island(algorithm.de(gen=1), Sphere(3), 4, seed=0)
+    with pytest.raises(ValueError):
+        isl.evolve(1)
+
+
+def test_select_is_greedy_and_ignores_nan():
+    prob = Sphere(3)
+    isl = island(algorithm.de(gen=1), prob, 6, seed=1)
+    pop = isl.population
+    pop.evaluate()
+    before = pop.f.copy()
+    trial = pop.X + 0.01
+    ft = prob.objfun_batch(trial)
+    ft[0] = np.nan
+    ft[1] = before[1] + 1.0
+    algorithm.de.select(pop, trial, ft)
+    assert pop.f[0] == before[0] and pop.f[1] == before[1]
+    assert (pop.f <= before).all()
+
+
+def test_archipelago_batches_islands_and_migrates():
+    Sphere.calls = Sphere.batches = 0
+    prob = Sphere(5)
+    algo = algorithm.de(gen=3, variant=3, f=0.85, cr=1.0)
+    archi = archipelago(algo, prob, 4, 10, topology=topology.ring(), seed=3)
+    archi.evolve(2)
+    archi.join()
+    # 1 initial evaluation + 2 rounds x 3 generations, each ONE batch of 4*10
+    assert Sphere.batches == 1 + 2 * 3
+    assert Sphere.calls == 40 * (1 + 6) == archi.evaluations
+    champs = archi.champions
+    assert len(champs) == 4
+    # after migration on a ring no island is worse than both neighbours' best
+    f = [c.f[0] for c in champs]
+    assert max(f) < 60.0
+
+
+def test_migration_replaces_worst_only_if_better():
+    prob = Sphere(2)
+    algo = algorithm.de(gen=0)
+    archi = archipelago(algo, prob, 2, 6, topology=topology.one_way_ring(), seed=5)
+    archi[0].set_x(0, [1.0, 1.0])          # optimum lives on island 0
+    archi.evolve(1)
+    assert archi[1].population.champion.f[0] == 0.0
+    assert archi[0].population.champion.f[0] == 0.0
+
+
+GLOO_SCRIPT = r"""
+import os, sys
+import numpy as np
+import torch.distributed as dist
+sys.path.insert(0, {repo!r})
+sys.path.insert(0, os.path.join({repo!r}, "tests"))
+from lassim_b200.pygmo import algorithm, archipelago, topology
+from test_de_archipelago import Sphere
+dist.init_process_group("gloo")
+rank = dist.get_rank()
+prob = Sphere(4)
+archi = archipelago(algorithm.de(gen=5, variant=3), prob, 4, 8,
+                    topology=topology.ring(), seed=11)
+archi.evolve(3)
+archi.join()
+f = np.array([c.f[0] for c in archi.champions])
+# every rank evaluated only its own islands
+assert archi.evaluations == 2 * 8 * (1 + 15), archi.evaluations
+np.save(os.path.join({out!r}, "champs_%d.npy" % rank), f)
+dist.destroy_process_group()
+"""
+
+
+def test_two_rank_gloo_islands(tmp_path):
+    script = tmp_path / "run.py"
+    script.write_text(GLOO_SCRIPT.format(repo=REPO, out=str(tmp_path)))
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29531")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+           "--nproc-per-node=2", "--master-addr", "127.0.0.1", "--master-port",
+           "29531", str(script)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    f0 = np.load(tmp_path / "champs_0.npy")
+    f1 = np.load(tmp_path / "champs_1.npy")
+    # both ranks end with the same view of all four islands' champions
+    np.testing.assert_array_equal(f0, f1)
+    assert f0.shape == (4,) and np.isfinite(f0).all()
