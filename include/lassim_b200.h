@@ -130,6 +130,41 @@ int lassim_last_end_states(lassim_handle *h, int N, double *E);
  * lassim_trajectories only slot 0 of each candidate is non-zero). */
 int lassim_last_traj_steps(lassim_handle *h, int N, unsigned int *steps);
 
+/*
+ * Evaluate N candidates WITHOUT allocating anything (no counterpart in the
+ * reference; added for hosts that cannot call cudaMalloc when they evaluate).
+ * Same result as lassim_eval_device's cost: dX[N*dim] and dcost[N] are DEVICE
+ * buffers the caller owns, the work is enqueued on `stream` (NULL = the
+ * handle's own stream) and the call returns after the launch.
+ *
+ * Who needs it: a process whose GPU memory already belongs to another
+ * framework's caching allocator (a library-side cudaMalloc would fail or
+ * fragment that pool), a latency-critical loop that cannot take the
+ * device-wide synchronisation cudaMalloc/cudaFree imply, a job held to a hard
+ * memory budget (MIG slice, MPS limit).  lassim_eval and lassim_eval_device
+ * grow their scratch with cudaMalloc whenever a batch is larger than any
+ * before; this entry point never calls cudaMalloc, cudaFree or any allocating
+ * routine.
+ *
+ * Its scratch is a fixed 8 MiB array inside the library image (each GPU that
+ * loads the library holds those 8 MiB until the process exits).  A batch needs
+ * about 8*N*(T*n + K*n) + 4*N*K + 56*N bytes (K = trajectories per candidate);
+ * for the Th2 example that is ~2.2 KB per candidate, i.e. up to ~3,700
+ * candidates per call.  Larger batches are rejected with LASSIM_E_INVALID and
+ * a message that names both sizes: split them or use lassim_eval_device.
+ *
+ * The first call on a device also looks up the array's device address; make
+ * that first call before starting any stream capture.  The problem must have
+ * been set (lassim_set_problem allocates; do it during set-up).  All calls in
+ * a process share the one array per GPU and it keeps the previous call's
+ * contents (the entry point clears the part that must start at zero), so two
+ * calls whose kernels overlap on the same GPU - different streams or different
+ * handles - race on it: order them.  lassim_last_end_states / _traj_steps do
+ * not see this path's scratch.
+ */
+int lassim_eval_device_noalloc(lassim_handle *h, int N, const double *dX,
+                               double *dcost, void *stream);
+
 /* Number of kernels this handle has launched so far. */
 long long lassim_launch_count(const lassim_handle *h);
 

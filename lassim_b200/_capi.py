@@ -59,6 +59,9 @@ def load_library():
                                        ctypes.c_void_p, ctypes.c_void_p,
                                        ctypes.c_void_p, ctypes.c_void_p,
                                        ctypes.c_void_p, ctypes.c_void_p]
+    lib.lassim_eval_device_noalloc.argtypes = [H, ctypes.c_int, ctypes.c_void_p,
+                                               ctypes.c_void_p, ctypes.c_void_p]
+    lib.lassim_eval_device_noalloc.restype = ctypes.c_int
     lib.lassim_trajectories.argtypes = [H, ctypes.c_int, c_double_p, c_double_p,
                                         c_int_p]
     lib.lassim_last_end_states.argtypes = [H, ctypes.c_int, c_double_p]
@@ -195,6 +198,14 @@ class Engine:
         self._check(self._lib.lassim_eval_device(
             self._h, int(N), x_ptr, cost_ptr, cost_main_ptr, pert_cost_ptr,
             status_ptr, counters_ptr, stream), "lassim_eval_device")
+
+    def eval_device_noalloc(self, N, x_ptr, cost_ptr, stream=None):
+        """Allocation-free variant of eval_device (cost only): for hosts that
+        cannot call cudaMalloc at evaluation time.  Scratch is a fixed 8 MiB
+        array inside the library; batches that do not fit raise LassimError.
+        Calls that overlap on one GPU race on that array - order them."""
+        self._check(self._lib.lassim_eval_device_noalloc(
+            self._h, int(N), x_ptr, cost_ptr, stream), "lassim_eval_device_noalloc")
 
     def trajectories(self, X, return_status=False):
         X = _f64(X)

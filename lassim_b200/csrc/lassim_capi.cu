@@ -527,3 +527,133 @@ int lassim_fp64_peak_probe(lassim_handle *h, int iters, double *tflops) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Evaluation without any allocation.
+//
+// Some callers of this library must not, or cannot, allocate device memory at
+// the moment they want a population evaluated: a host process in which another
+// framework's caching allocator already owns (almost) all of the GPU, so a raw
+// cudaMalloc from a library fails or fragments its pool; a serving or control
+// loop that cannot afford the device-wide synchronisation cudaMalloc/cudaFree
+// imply while other streams are busy; a job confined to a hard memory budget
+// (MIG slice, MPS limit) that was sized without this library's scratch.  For
+// them the scratch of the evaluation kernel lives in a fixed array that is part
+// of the loaded library image: every GPU that loads liblassim_b200.so holds
+// LASSIM_NOALLOC_SCRATCH_BYTES of it until the process exits.
+//
+// In host code the array's name is only a stand-in for the symbol, not a
+// device address; the address is resolved once per device with
+// cudaGetSymbolAddress and cached here.
+// ---------------------------------------------------------------------------
+#define LASSIM_NOALLOC_SCRATCH_BYTES (8u << 20)
+#define LASSIM_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[LASSIM_NOALLOC_SCRATCH_BYTES];
+static unsigned char *g_noalloc_addr[LASSIM_NOALLOC_MAX_DEVICES];   // per device, set once
+
+namespace {
+
+struct NoallocLayout {
+    size_t off_done, off_status, off_counters, zero_bytes;
+    size_t off_cost_main, off_pert_cost, off_steps, off_Y, off_E, bytes;
+};
+
+size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+NoallocLayout noalloc_layout(int N, int T, int K, int n) {
+    NoallocLayout L;
+    L.off_done = 16;                                       // [0,16): work counter
+    L.off_status = L.off_done + sizeof(int) * (size_t)N;
+    L.off_counters = (L.off_status + sizeof(int) * (size_t)N + 15) & ~(size_t)15;
+    L.zero_bytes = L.off_counters + sizeof(unsigned long long) * 3 * (size_t)N;
+    L.off_cost_main = align256(L.zero_bytes);
+    L.off_pert_cost = align256(L.off_cost_main + sizeof(double) * (size_t)N);
+    L.off_steps = align256(L.off_pert_cost + sizeof(double) * (size_t)N);
+    L.off_Y = align256(L.off_steps + sizeof(unsigned) * (size_t)N * K);
+    L.off_E = align256(L.off_Y + sizeof(double) * (size_t)N * T * n);
+    L.bytes = L.off_E + sizeof(double) * (size_t)N * K * n;
+    return L;
+}
+
+}  // namespace
+
+extern "C" int lassim_eval_device_noalloc(lassim_handle *h, int N, const double *dX,
+                                          double *dcost, void *stream) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->has_problem) return fail(h, LASSIM_E_STATE, "eval before set_problem");
+    if (N < 0 || (N > 0 && (!dX || !dcost)))
+        return fail(h, LASSIM_E_INVALID, "eval_device_noalloc: N=%d, X or cost is NULL", N);
+    if (N == 0) return LASSIM_OK;
+    if (h->device < 0 || h->device >= LASSIM_NOALLOC_MAX_DEVICES)
+        return fail(h, LASSIM_E_UNSUPPORTED, "device index %d is beyond the %d devices the "
+                    "allocation-free path keeps an address for", h->device,
+                    LASSIM_NOALLOC_MAX_DEVICES);
+    const int K = h->K, n = h->n, T = h->T;
+    const NoallocLayout L = noalloc_layout(N, T, K, n);
+    if (L.bytes > (size_t)LASSIM_NOALLOC_SCRATCH_BYTES) {
+        const size_t per = 8 * ((size_t)T * n + (size_t)K * n) + 4 * (size_t)K + 56;
+        return fail(h, LASSIM_E_INVALID,
+                    "eval_device_noalloc: %d candidates of this problem need %zu bytes of "
+                    "scratch but the built-in scratch holds %u bytes (about %zu candidates); "
+                    "split the batch or use lassim_eval_device",
+                    N, L.bytes, (unsigned)LASSIM_NOALLOC_SCRATCH_BYTES,
+                    ((size_t)LASSIM_NOALLOC_SCRATCH_BYTES - 2048) / per);
+    }
+    CU(cudaSetDevice(h->device));
+    // one-time set-up on this device: turn the symbol into a device address
+    if (!g_noalloc_addr[h->device]) {
+        unsigned char *addr = nullptr;
+        CU(cudaGetSymbolAddress((void **)&addr, g_noalloc_scratch));
+        if (!addr)
+            return fail(h, LASSIM_E_CUDA, "cudaGetSymbolAddress returned a null address");
+        g_noalloc_addr[h->device] = addr;
+    }
+    unsigned char *base = g_noalloc_addr[h->device];
+    KernelChoice kc;
+    if (!choose_kernel(n, &kc))
+        return fail(h, LASSIM_E_UNSUPPORTED,
+                    "state size n=%d is outside the kernels built (n <= 32)", n);
+    cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+    // the array keeps whatever the previous call left: clear what must be zero
+    CU(cudaMemsetAsync(base, 0, L.zero_bytes, s));
+
+    DevProblem P;
+    P.n = n; P.T = T; P.K = K; P.U = h->U; P.dim = h->dim; P.nnz = h->nnz;
+    P.times = h->d_times.p; P.y0 = h->d_y0.p; P.data = h->d_data.p;
+    P.sigma2 = h->d_sigma2.p; P.kidx = h->d_kidx.p;
+    P.pert = (K > 1) ? h->d_pert.p : nullptr;
+    P.traj_prefix = h->d_traj_prefix.p; P.traj_tt = h->d_traj_tt.p;
+    P.knock_ctrl = h->d_knock_ctrl.p;
+    P.pert_factor = h->pert_factor; P.rtol = h->rtol; P.atol = h->atol;
+    P.max_steps = (unsigned int)(h->max_steps > 4000000000LL ? 4000000000LL : h->max_steps);
+
+    DevBatch B;
+    B.N = N; B.mode = 0; B.X = dX;
+    B.cost = dcost;                                           // straight into the caller's buffer
+    B.work_counter = reinterpret_cast<unsigned int *>(base);
+    B.done = reinterpret_cast<int *>(base + L.off_done);
+    B.status = reinterpret_cast<int *>(base + L.off_status);
+    B.counters = reinterpret_cast<unsigned long long *>(base + L.off_counters);
+    B.cost_main = reinterpret_cast<double *>(base + L.off_cost_main);
+    B.pert_cost = reinterpret_cast<double *>(base + L.off_pert_cost);
+    B.traj_steps = reinterpret_cast<unsigned int *>(base + L.off_steps);
+    B.Y = reinterpret_cast<double *>(base + L.off_Y);
+    B.E = reinterpret_cast<double *>(base + L.off_E);
+    B.order = nullptr;
+
+    const int groups_per_cta = kThreads / kc.G;
+    const size_t smem = (64 + (size_t)groups_per_cta * 2 * (kc.G * kc.R + 2)) * sizeof(double);
+    int per_sm = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kc.fn, kThreads, smem));
+    if (per_sm < 1) per_sm = 1;
+    const long long work = (long long)N * K;
+    long long blocks = (work + groups_per_cta - 1) / groups_per_cta;
+    const long long resident = (long long)h->sm_count * per_sm;
+    if (blocks > resident) blocks = resident;
+    kc.fn<<<(unsigned)blocks, kThreads, smem, s>>>(P, B);
+    CU(cudaGetLastError());
+    h->launches += 1;
+    return LASSIM_OK;
+}
+
