@@ -85,7 +85,8 @@ struct DevBatch {
 #define DP_E6 (22.0 / 525.0)
 #define DP_E7 (-1.0 / 40.0)
 
-constexpr int kThreads = 128;
+// threads per CTA
+constexpr int threads_for(int G) { return G == 4 ? 256 : 128; }
 
 template <int G>
 __device__ __forceinline__ double group_max(double v, unsigned gmask) {
@@ -103,25 +104,33 @@ __device__ __forceinline__ double group_sum(double v, unsigned gmask) {
     return v;
 }
 
-// 2^(j/64), j = 0..63, filled by the host at load time.
+// 2^(j/64), j = 0..63, filled by the host when the engine is created.
 __constant__ double c_exp2_table[64];
 
-constexpr double kNegLog2e = -1.4426950408889634074;
+// With the fast logistic the rows of W are pre-scaled by -log2(e) at load, so
+// the mat-vec delivers t = -z*log2(e) directly.
+constexpr double kSigScale = -1.4426950408889634074;
 
-// Exact-libm activation vmax / (1 + exp(-z)) with the reference's overflow
-// behaviour: exp(-z) -> +inf gives 0 (common_functions.pyx:37-39).  Kept as the
-// A/B check of the fast path below (LASSIM_EXACT_MATH=1).
+// Exact-libm logistic with the reference's overflow behaviour: exp(-z) -> +inf
+// gives 0 (common_functions.pyx:37-39).  A/B check of the fast path
+// (LASSIM_EXACT_MATH=1).
 __device__ __forceinline__ double logistic_libm(double z) {
     return 1.0 / (1.0 + exp(-z));
 }
 
 // 1 / (1 + 2^t), t = -z*log2(e).  2^t = 2^n * T[j] * 2^f with t = n + j/64 + f,
 // |f| <= 2^-7 (degree-5 Taylor for 2^f - 1, truncation 4e-17); the reciprocal
-// is an SFU seed (MUFU.RCP64H) refined by two FP64 Newton steps.  ~3 ulp.  t is
-// clamped to +-1000: below, 2^t vanishes next to 1; above, the result is
+// is an SFU seed (MUFU.RCP64H) refined by one third-order FP64 step.  ~3 ulp.
+// |t| is clamped to 1000: below, 2^t vanishes next to 1; above, the result is
 // < 1e-301 where the reference returns vmax*exp(z) or 0 after overflow.
-__device__ __forceinline__ double logistic_exp2(double t, const double *tab) {
-    t = fmin(fmax(t, -1000.0), 1000.0);
+__device__ __forceinline__ double logistic_fast(double t, const double *tab) {
+    // clamp (also catches NaN/inf) with integer ops on the high word: off the
+    // FP64 pipe, shorter than two compare+select pairs on the dependent chain
+    {
+        const int hi = __double2hiint(t);
+        if ((hi & 0x7fffffff) >= 0x408f4000)
+            t = __hiloint2double((hi & 0x80000000) | 0x408f4000, 0);
+    }
     const double kMagic = 105553116266496.0;   // 1.5 * 2^46: ulp = 1/64
     const double s = t + kMagic;
     const int ki = __double2loint(s);
@@ -137,30 +146,26 @@ __device__ __forceinline__ double logistic_exp2(double t, const double *tab) {
     const double d = 1.0 + e;
     double r;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
-    r = fma(r, fma(-d, r, 1.0), r);
-    r = fma(r, fma(-d, r, 1.0), r);
-    return r;
+    // one third-order step: r*(1 + e0 + e0^2), e0 = 1 - d*r (seed error 2^-23
+    // -> 2^-69), one dependent FMA less than two Newton steps
+    const double e0 = fma(-d, r, 1.0);
+    return fma(r, fma(e0, e0, e0), r);
 }
 
-// f = -lambda*ys + vmax*sigmoid(W ys); ys of the whole group goes through buf.
-// With FAST the rows of W arrive pre-scaled by -log2(e).  NC = columns of W
+// sg = sigmoid(W ys) for this lane's genes; ys of the whole group goes through
+// buf.  With FAST the rows of W arrive pre-scaled by -log2(e).  NC = columns of W
 // actually used (n rounded up to 4).
-template <int G, int R, int NC, bool FAST>
-__device__ __forceinline__ void rhs_eval(const double (&ys)[R], double (&f)[R],
-                                         const double (&W)[R][NC],
-                                         const double (&lam)[R],
-                                         const double (&vm)[R], double *buf,
-                                         const double *tab, unsigned gmask,
-                                         int lg) {
+template <int G, int R, int NC, bool FAST, bool WHOLE_WARP>
+__device__ __forceinline__ void rhs_sigma(const double (&ys)[R], double (&sg)[R],
+                                          const double (&W)[R][NC], double *buf,
+                                          const double *tab, unsigned gmask,
+                                          int lg) {
 #pragma unroll
     for (int r = 0; r < R; ++r) buf[lg * R + r] = ys[r];
-    __syncwarp(gmask);
-    double a0[R], a1[R], a2[R], a3[R], ly[R];
+    if (WHOLE_WARP) __syncwarp(); else __syncwarp(gmask);
+    double a0[R], a1[R], a2[R], a3[R];
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-        a0[r] = 0.0; a1[r] = 0.0; a2[r] = 0.0; a3[r] = 0.0;
-        ly[r] = -lam[r] * ys[r];
-    }
+    for (int r = 0; r < R; ++r) { a0[r] = 0.0; a1[r] = 0.0; a2[r] = 0.0; a3[r] = 0.0; }
 #pragma unroll
     for (int j = 0; j < NC; j += 4) {
         const double2 v = *reinterpret_cast<const double2 *>(buf + j);
@@ -176,21 +181,12 @@ __device__ __forceinline__ void rhs_eval(const double (&ys)[R], double (&f)[R],
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         const double z = (a0[r] + a1[r]) + (a2[r] + a3[r]);
-        const double sg = FAST ? logistic_exp2(z, tab) : logistic_libm(z);
-        f[r] = fma(vm[r], sg, ly[r]);
+        sg[r] = FAST ? logistic_fast(z, tab) : logistic_libm(z);
     }
 }
 
-// Max over the lanes of `gmask` of a non-negative double (NaN -> +inf), through
-// one REDUX on the float bit pattern (IEEE order = unsigned order for >= 0).
-__device__ __forceinline__ float group_max_nonneg(double q, unsigned gmask) {
-    float qf = (float)q;
-    if (!(q <= 3.0e38)) qf = CUDART_INF_F;   // NaN, inf or beyond float range
-    return __uint_as_float(__reduce_max_sync(gmask, __float_as_uint(qf)));
-}
-
 template <int G, int R, int NC, bool FAST>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(threads_for(G))
 grn_cost_kernel(const DevProblem P, const DevBatch B) {
     constexpr int NP = G * R;
     constexpr int STRIDE = NP + 2;   // 16 B skew between groups: no bank conflicts
@@ -228,10 +224,19 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
     double t = 0.0, h = 0.0, tend = 0.0;
     const double *tl = P.times;
 
-#define LASSIM_RHS(in, out)                                                    \
+    // LASSIM_SIG_G: only this group's lanes take part (trajectory set-up, which
+    // groups of one warp reach at different times).  LASSIM_SIG: the whole warp
+    // executes it together (the step loop is warp-uniform).
+#define LASSIM_SIG_G(in, out)                                                  \
     do {                                                                       \
-        rhs_eval<G, R, NC, FAST>(in, out, W, lam, vm, ybuf + cur * STRIDE,     \
-                                 tab, gmask, lg);                              \
+        rhs_sigma<G, R, NC, FAST, false>(in, out, W, ybuf + cur * STRIDE, tab, \
+                                         gmask, lg);                           \
+        cur ^= 1;                                                              \
+    } while (0)
+#define LASSIM_SIG(in, out)                                                    \
+    do {                                                                       \
+        rhs_sigma<G, R, NC, FAST, true>(in, out, W, ybuf + cur * STRIDE, tab,  \
+                                        gmask, lg);                            \
         cur ^= 1;                                                              \
     } while (0)
 
@@ -266,7 +271,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                             const int id = P.kidx[g * n + j];
                             if (id >= 0) wv = x[2 * n + id];
                         }
-                        W[r][j] = FAST ? wv * kNegLog2e : wv;
+                        W[r][j] = FAST ? wv * kSigScale : wv;
                     }
                 }
                 if (k == 0) { tl = P.times; nt = P.T; }
@@ -283,7 +288,10 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                 }
                 // first derivative + starting step (Hairer/Norsett/Wanner II.4,
                 // max-norm variant)
-                LASSIM_RHS(y, k1);
+                double sg[R];
+                LASSIM_SIG_G(y, sg);
+#pragma unroll
+                for (int r = 0; r < R; ++r) k1[r] = fma(vm[r], sg[r], -lam[r] * y[r]);
                 double d0 = 0.0, d1 = 0.0;
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
@@ -296,7 +304,9 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                 const double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
 #pragma unroll
                 for (int r = 0; r < R; ++r) ys[r] = fma(h0, k1[r], y[r]);
-                LASSIM_RHS(ys, k2);
+                LASSIM_SIG_G(ys, sg);
+#pragma unroll
+                for (int r = 0; r < R; ++r) k2[r] = fma(vm[r], sg[r], -lam[r] * ys[r]);
                 double d2 = 0.0;
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
@@ -314,113 +324,191 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
         }
         if (!__any_sync(0xffffffffu, active)) break;
 
-        if (active && ti < nt) {
+        {
             // ---------------------------------------------------- one attempt
+            // Executed by the whole warp together (no per-group branch): a
+            // group without a live trajectory computes on stale registers and
+            // its results are discarded.  This keeps __syncwarp and the
+            // shuffles full-mask and the groups of a warp in lockstep.
+            const bool live = active && ti < nt;
             double hs = h;
             bool hit = false;
             if (t + 1.01 * hs >= tend) { hs = tend - t; hit = true; }
-            double part[R];   // terms of the next stage that are already known
+            // Stage s needs ys = y + hs*sum_j a_sj k_j with k_{s-1} = vm*sg + ly
+            // (ly = -lambda*ys_{s-1}) only just computed.  Everything except sg is
+            // known before the logistic finishes, so it is folded into q and the
+            // dependent chain from sg to the next stage state is ONE fma:
+            //   ys = fma(hs*a_last*vm, sg, q),  q = y + hs*sum_{j<s-1} + hs*a_last*ly
+            double sg[R], q[R], ly[R], cv[R];
 #pragma unroll
             for (int r = 0; r < R; ++r) ys[r] = fma(hs * DP_A21, k1[r], y[r]);
-            LASSIM_RHS(ys, k2);
+            {   // ---- stage 2 -> state of stage 3
+                const double hl = hs * DP_A32;
 #pragma unroll
-            for (int r = 0; r < R; ++r)
-                ys[r] = fma(hs, fma(DP_A32, k2[r], DP_A31 * k1[r]), y[r]);
+                for (int r = 0; r < R; ++r) {
+                    ly[r] = -lam[r] * ys[r];
+                    cv[r] = hl * vm[r];
+                    q[r] = fma(hl, ly[r], fma(hs * DP_A31, k1[r], y[r]));
+                }
+                LASSIM_SIG(ys, sg);
 #pragma unroll
-            for (int r = 0; r < R; ++r) part[r] = fma(DP_A42, k2[r], DP_A41 * k1[r]);
-            LASSIM_RHS(ys, k3);
+                for (int r = 0; r < R; ++r) {
+                    ys[r] = fma(cv[r], sg[r], q[r]);
+                    k2[r] = fma(vm[r], sg[r], ly[r]);
+                }
+            }
+            {   // ---- stage 3 -> state of stage 4
+                const double hl = hs * DP_A43;
 #pragma unroll
-            for (int r = 0; r < R; ++r)
-                ys[r] = fma(hs, fma(DP_A43, k3[r], part[r]), y[r]);
+                for (int r = 0; r < R; ++r) {
+                    ly[r] = -lam[r] * ys[r];
+                    cv[r] = hl * vm[r];
+                    q[r] = fma(hl, ly[r],
+                               fma(hs, fma(DP_A42, k2[r], DP_A41 * k1[r]), y[r]));
+                }
+                LASSIM_SIG(ys, sg);
 #pragma unroll
-            for (int r = 0; r < R; ++r)
-                part[r] = fma(DP_A53, k3[r], fma(DP_A52, k2[r], DP_A51 * k1[r]));
-            LASSIM_RHS(ys, k4);
+                for (int r = 0; r < R; ++r) {
+                    ys[r] = fma(cv[r], sg[r], q[r]);
+                    k3[r] = fma(vm[r], sg[r], ly[r]);
+                }
+            }
+            {   // ---- stage 4 -> state of stage 5
+                const double hl = hs * DP_A54;
 #pragma unroll
-            for (int r = 0; r < R; ++r)
-                ys[r] = fma(hs, fma(DP_A54, k4[r], part[r]), y[r]);
+                for (int r = 0; r < R; ++r) {
+                    ly[r] = -lam[r] * ys[r];
+                    cv[r] = hl * vm[r];
+                    q[r] = fma(hl, ly[r],
+                               fma(hs, fma(DP_A53, k3[r],
+                                           fma(DP_A52, k2[r], DP_A51 * k1[r])), y[r]));
+                }
+                LASSIM_SIG(ys, sg);
 #pragma unroll
-            for (int r = 0; r < R; ++r)
-                part[r] = fma(DP_A64, k4[r],
-                              fma(DP_A63, k3[r], fma(DP_A62, k2[r], DP_A61 * k1[r])));
-            LASSIM_RHS(ys, k5);
+                for (int r = 0; r < R; ++r) {
+                    ys[r] = fma(cv[r], sg[r], q[r]);
+                    k4[r] = fma(vm[r], sg[r], ly[r]);
+                }
+            }
+            {   // ---- stage 5 -> state of stage 6
+                const double hl = hs * DP_A65;
 #pragma unroll
-            for (int r = 0; r < R; ++r)
-                ys[r] = fma(hs, fma(DP_A65, k5[r], part[r]), y[r]);
+                for (int r = 0; r < R; ++r) {
+                    ly[r] = -lam[r] * ys[r];
+                    cv[r] = hl * vm[r];
+                    q[r] = fma(hl, ly[r],
+                               fma(hs, fma(DP_A64, k4[r],
+                                           fma(DP_A63, k3[r],
+                                               fma(DP_A62, k2[r], DP_A61 * k1[r]))), y[r]));
+                }
+                LASSIM_SIG(ys, sg);
 #pragma unroll
-            for (int r = 0; r < R; ++r)
-                part[r] = fma(DP_B5, k5[r],
-                              fma(DP_B4, k4[r], fma(DP_B3, k3[r], DP_B1 * k1[r])));
-            LASSIM_RHS(ys, k6);
-            double epart[R], isc[R];
+                for (int r = 0; r < R; ++r) {
+                    ys[r] = fma(cv[r], sg[r], q[r]);
+                    k5[r] = fma(vm[r], sg[r], ly[r]);
+                }
+            }
+            {   // ---- stage 6 -> the 5th-order solution yn
+                const double hl = hs * DP_B6;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    ly[r] = -lam[r] * ys[r];
+                    cv[r] = hl * vm[r];
+                    q[r] = fma(hl, ly[r],
+                               fma(hs, fma(DP_B5, k5[r],
+                                           fma(DP_B4, k4[r],
+                                               fma(DP_B3, k3[r], DP_B1 * k1[r]))), y[r]));
+                }
+                LASSIM_SIG(ys, sg);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    yn[r] = fma(cv[r], sg[r], q[r]);
+                    k6[r] = fma(vm[r], sg[r], ly[r]);
+                }
+            }
+            // ---- stage 7 (FSAL) and the error estimate, again one fma after sg:
+            //   e = hs*(E1 k1 + E3 k3 + .. + E6 k6 + E7 k7),  k7 = vm*sg + ly
+            double isc[R], eq[R], ce[R];
+            {
+                const double hl = hs * DP_E7;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    ly[r] = -lam[r] * yn[r];
+                    ce[r] = hl * vm[r];
+                    eq[r] = fma(hl, ly[r],
+                                hs * fma(DP_E6, k6[r],
+                                         fma(DP_E5, k5[r],
+                                             fma(DP_E4, k4[r],
+                                                 fma(DP_E3, k3[r], DP_E1 * k1[r])))));
+                    // the error weight only needs y and yn: off the critical path
+                    isc[r] = 1.0 / fma(rtol, fmax(fabs(y[r]), fabs(yn[r])), atol);
+                }
+                LASSIM_SIG(yn, sg);
+            }
+            double qd = 0.0;
 #pragma unroll
             for (int r = 0; r < R; ++r) {
-                yn[r] = fma(hs, fma(DP_B6, k6[r], part[r]), y[r]);
-                epart[r] = fma(DP_E6, k6[r],
-                               fma(DP_E5, k5[r],
-                                   fma(DP_E4, k4[r], fma(DP_E3, k3[r], DP_E1 * k1[r]))));
+                const double e = fma(ce[r], sg[r], eq[r]);
+                k7[r] = fma(vm[r], sg[r], ly[r]);
+                qd = fmax(qd, fabs(e) * isc[r]);      // fmax drops NaN: checked next
+                if (e != e) qd = CUDART_INF;
             }
-            // the error weight only needs y and yn: off the critical path
+            // max over the group as a float (IEEE order of non-negative floats);
+            // xor offsets below G stay inside the group, so full-mask shuffles do
+            float qf = (qd <= 3.0e38) ? (float)qd : CUDART_INF_F;
 #pragma unroll
-            for (int r = 0; r < R; ++r)
-                isc[r] = 1.0 / fma(rtol, fmax(fabs(y[r]), fabs(yn[r])), atol);
-            LASSIM_RHS(yn, k7);
-            double q = 0.0;
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const double e = hs * fma(DP_E7, k7[r], epart[r]);
-                double qr = fabs(e) * isc[r];
-                if (!(qr <= 1.79e308)) qr = CUDART_INF;   // NaN or inf
-                q = fmax(q, qr);
-            }
-            const float qf = group_max_nonneg(q, gmask);
+            for (int o = G / 2; o > 0; o >>= 1)
+                qf = fmaxf(qf, __shfl_xor_sync(0xffffffffu, qf, o));
 
-            bool finished = false;
             const float qc = fminf(fmaxf(qf, 1e-30f), 3.0e38f);
             const float fac0 = 0.9f * exp2f(-0.2f * __log2f(qc));
-            if (qf <= 1.0f) {
-                ++nacc;
-                t = hit ? tend : t + hs;
+            const bool accept = qf <= 1.0f;
+            bool failed = false;
+            if (live) {
+                if (accept) {
+                    ++nacc;
+                    t = hit ? tend : t + hs;
 #pragma unroll
-                for (int r = 0; r < R; ++r) { y[r] = yn[r]; k1[r] = k7[r]; }
-                float fac = fminf(10.0f, fmaxf(0.2f, fac0));
-                if (rejected) fac = fminf(fac, 1.0f);
-                rejected = false;
-                const double hnew = hs * (double)fac;
-                h = hit ? fmax(hnew, h) : hnew;
-                if (hit) {
+                    for (int r = 0; r < R; ++r) { y[r] = yn[r]; k1[r] = k7[r]; }
+                    float fac = fminf(10.0f, fmaxf(0.2f, fac0));
+                    if (rejected) fac = fminf(fac, 1.0f);
+                    rejected = false;
+                    const double hnew = hs * (double)fac;
+                    h = hit ? fmax(hnew, h) : hnew;
+                    if (hit) {
+                        if (k == 0) {
+                            double *Yc = B.Y + ((size_t)c * P.T + ti) * n;
+#pragma unroll
+                            for (int r = 0; r < R; ++r)
+                                if (gene_ok[r]) Yc[lg * R + r] = y[r];
+                        }
+                        ++ti;
+                        if (ti < nt) tend = tl[ti];
+                    }
+                } else {
+                    ++nrej;
+                    rejected = true;
+                    h = hs * (double)fmaxf(0.2f, fminf(fac0, 1.0f));
+                    if (!(fabs(h) > 1e-290) || t + h == t) { st |= 2; failed = true; }
+                }
+                if (!failed && ti < nt && nacc + nrej >= P.max_steps) {
+                    st |= 1;
+                    failed = true;
+                }
+                if (failed) {
+                    // failed trajectory: poison what it would have produced
+#pragma unroll
+                    for (int r = 0; r < R; ++r) y[r] = CUDART_NAN;
                     if (k == 0) {
-                        double *Yc = B.Y + ((size_t)c * P.T + ti) * n;
+                        for (int s = ti; s < nt; ++s) {
+                            double *Yc = B.Y + ((size_t)c * P.T + s) * n;
 #pragma unroll
-                        for (int r = 0; r < R; ++r)
-                            if (gene_ok[r]) Yc[lg * R + r] = y[r];
+                            for (int r = 0; r < R; ++r)
+                                if (gene_ok[r]) Yc[lg * R + r] = CUDART_NAN;
+                        }
                     }
-                    ++ti;
-                    if (ti < nt) tend = tl[ti];
+                    ti = nt;
                 }
-            } else {
-                ++nrej;
-                rejected = true;
-                h = hs * (double)fmaxf(0.2f, fminf(fac0, 1.0f));
-                if (!(fabs(h) > 1e-290) || t + h == t) { st |= 2; finished = true; }
-            }
-            if (!finished && ti < nt && nacc + nrej >= P.max_steps) {
-                st |= 1;
-                finished = true;
-            }
-            if (finished) {
-                // failed trajectory: poison what it would have produced
-#pragma unroll
-                for (int r = 0; r < R; ++r) y[r] = CUDART_NAN;
-                if (k == 0) {
-                    for (int s = ti; s < nt; ++s) {
-                        double *Yc = B.Y + ((size_t)c * P.T + s) * n;
-#pragma unroll
-                        for (int r = 0; r < R; ++r)
-                            if (gene_ok[r]) Yc[lg * R + r] = CUDART_NAN;
-                    }
-                }
-                ti = nt;
             }
         }
 
@@ -526,7 +614,8 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
             }
         }
     }
-#undef LASSIM_RHS
+#undef LASSIM_SIG
+#undef LASSIM_SIG_G
 }
 
 // Register-resident DFMA throughput probe (roofline denominator).

@@ -124,7 +124,15 @@ typedef void (*kernel_fn)(const DevProblem, const DevBatch);
 struct KernelChoice {
     kernel_fn fn;
     int G, R;
+    bool fast;
 };
+
+// dynamic shared memory of one CTA: the 2^(j/64) table + the groups'
+// double-buffered exchange lines
+size_t smem_bytes(const KernelChoice &kc) {
+    const int groups_per_cta = threads_for(kc.G) / kc.G;
+    return (64 + (size_t)groups_per_cta * 2 * (kc.G * kc.R + 2)) * sizeof(double);
+}
 
 template <int G, int R, bool FAST>
 kernel_fn pick_columns(int n) {
@@ -146,20 +154,16 @@ bool choose_kernel(int n, KernelChoice *out) {
     const int want = env ? atoi(env) : 0;
     const char *ex = getenv("LASSIM_EXACT_MATH");
     const bool fast = !(ex && atoi(ex) != 0);
-    if (n <= 12 && want == 4) {
-        *out = {fast ? pick_columns<4, 3, true>(n) : pick_columns<4, 3, false>(n), 4, 3};
-        return true;
-    }
-    if (n <= 16 && want == 8) {
-        *out = {fast ? pick_columns<8, 2, true>(n) : pick_columns<8, 2, false>(n), 8, 2};
+    if (n <= 12 && want == 4) {   // four lanes x three genes: throughput shape
+        *out = {pick_columns<4, 3, true>(n), 4, 3, true};
         return true;
     }
     if (n <= 16) {
-        *out = {fast ? pick_columns<16, 1, true>(n) : pick_columns<16, 1, false>(n), 16, 1};
+        *out = {fast ? pick_columns<16, 1, true>(n) : pick_columns<16, 1, false>(n), 16, 1, fast};
         return true;
     }
     if (n <= 32) {
-        *out = {fast ? pick_columns<32, 1, true>(n) : pick_columns<32, 1, false>(n), 32, 1};
+        *out = {fast ? pick_columns<32, 1, true>(n) : pick_columns<32, 1, false>(n), 32, 1, fast};
         return true;
     }
     return false;
@@ -205,10 +209,12 @@ int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
     B.counters = reinterpret_cast<unsigned long long *>(h->d_zero.p + z.off_counters);
     B.Y = dY; B.E = h->d_E.p; B.traj_steps = h->d_steps.p; B.order = nullptr;
 
-    const int groups_per_cta = kThreads / kc.G;
-    const size_t smem = (64 + (size_t)groups_per_cta * 2 * (kc.G * kc.R + 2)) * sizeof(double);
+    const int groups_per_cta = threads_for(kc.G) / kc.G;
+    const size_t smem = smem_bytes(kc);
+    CU(cudaFuncSetAttribute((const void *)kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            (int)smem));
     int per_sm = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kc.fn, kThreads, smem));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kc.fn, threads_for(kc.G), smem));
     if (per_sm < 1) per_sm = 1;
     const long long work = (long long)N * (mode == 0 ? K : 1);
     long long blocks = (work + groups_per_cta - 1) / groups_per_cta;
@@ -217,7 +223,7 @@ int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
     if (blocks < 1) blocks = 1;
 
     CU(cudaEventRecord(h->ev0, s));
-    kc.fn<<<(unsigned)blocks, kThreads, smem, s>>>(P, B);
+    kc.fn<<<(unsigned)blocks, threads_for(kc.G), smem, s>>>(P, B);
     CU(cudaGetLastError());
     CU(cudaEventRecord(h->ev1, s));
     h->timed = true;
@@ -642,16 +648,18 @@ extern "C" int lassim_eval_device_noalloc(lassim_handle *h, int N, const double 
     B.E = reinterpret_cast<double *>(base + L.off_E);
     B.order = nullptr;
 
-    const int groups_per_cta = kThreads / kc.G;
-    const size_t smem = (64 + (size_t)groups_per_cta * 2 * (kc.G * kc.R + 2)) * sizeof(double);
+    const int groups_per_cta = threads_for(kc.G) / kc.G;
+    const size_t smem = smem_bytes(kc);
+    CU(cudaFuncSetAttribute((const void *)kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            (int)smem));
     int per_sm = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kc.fn, kThreads, smem));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kc.fn, threads_for(kc.G), smem));
     if (per_sm < 1) per_sm = 1;
     const long long work = (long long)N * K;
     long long blocks = (work + groups_per_cta - 1) / groups_per_cta;
     const long long resident = (long long)h->sm_count * per_sm;
     if (blocks > resident) blocks = resident;
-    kc.fn<<<(unsigned)blocks, kThreads, smem, s>>>(P, B);
+    kc.fn<<<(unsigned)blocks, threads_for(kc.G), smem, s>>>(P, B);
     CU(cudaGetLastError());
     h->launches += 1;
     return LASSIM_OK;
