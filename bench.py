@@ -212,11 +212,11 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     p = load_th2()
-    n, nnz = 12, int(p["mask"].sum())
-    flops_per_attempt = 12 * nnz + 90 * n
     X = population(p, rank)
     eng = Engine(local)
+    eng.set_method(args.method)
     eng.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"], p["pert"], PERT_FACTOR)
+    flops_per_attempt = eng.flops_per_attempt      # SURVEY.md 8d, per integrator
 
     dX = torch.from_numpy(X).cuda()
     dcost = torch.empty(POP, dtype=torch.float64, device="cuda")
@@ -298,8 +298,10 @@ def run_ours(args):
             "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(world, "flushed between timed steps (256 MiB write); "
-                                             "per-step CUDA events on the launching stream"),
+            "config": dict(workload_config(world, "flushed between timed steps (256 MiB write); "
+                                                  "per-step CUDA events on the launching stream"),
+                           integrator={"dop853": "Dormand-Prince 8(5,3)",
+                                       "dp45": "Dormand-Prince 5(4)"}[args.method]),
             "results_ok": ok,
             "e2e": {"value": e2e_value, "unit": UNIT,
                     "h2d_bytes_per_step": int(X.nbytes), "d2h_bytes_per_step": int(POP * 8),
@@ -309,7 +311,7 @@ def run_ours(args):
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak,
                          "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
                          "traffic": None,
-                         "kernel": "grn_cost_kernel<16,1,12,true>", "kernel_ms": k_ms,
+                         "kernel": eng.kernel_name, "kernel_ms": k_ms,
                          "step_attempts_per_launch": float(np.mean(attempts)),
                          "flops_per_attempt": flops_per_attempt,
                          "peak_source": "in-run DFMA probe kernel (MEASURED_PEAKS.json has "
@@ -337,6 +339,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--method", default=os.environ.get("LASSIM_METHOD", "dop853"),
+                    choices=["dop853", "dp45"], help="integrator of the CUDA path")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

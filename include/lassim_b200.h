@@ -82,6 +82,14 @@ int lassim_set_mask(lassim_handle *h, const unsigned char *mask);
 int lassim_set_tolerances(lassim_handle *h, double rtol, double atol,
                           long long max_steps);
 
+/* Integrator: LASSIM_METHOD_DOP853 = Dormand-Prince 8(5,3) (default: about 5x
+ * fewer steps than the 5(4) pair at these tolerances and closer to the
+ * converged answer) or LASSIM_METHOD_DP45 = Dormand-Prince 5(4).  Both use the
+ * same error weights, norm and tolerances.  (The reference has one integrator,
+ * LSODA - variable order up to 12 - common_functions.pyx:86-90.) */
+enum { LASSIM_METHOD_DP45 = 0, LASSIM_METHOD_DOP853 = 1 };
+int lassim_set_method(lassim_handle *h, int method);
+
 /* Current decision-vector length (2n + nnz), trajectories per candidate
  * (1 + unique time pairs + n when a knock-down matrix is set, else 1). */
 int lassim_dim(const lassim_handle *h);
@@ -164,6 +172,13 @@ int lassim_last_traj_steps(lassim_handle *h, int N, unsigned int *steps);
  */
 int lassim_eval_device_noalloc(lassim_handle *h, int N, const double *dX,
                                double *dcost, void *stream);
+
+/* Algorithmic FP64 flops of one step attempt of one trajectory with the current
+ * problem and integrator (roofline numerator): 12*nnz + 90*n for
+ * the 5(4) pair, 24*nnz + 212*n for the 8(5,3) pair.  Name of the kernel the
+ * current problem dispatches to.  (No reference counterpart.) */
+long long lassim_flops_per_attempt(const lassim_handle *h);
+const char *lassim_kernel_name(lassim_handle *h);
 
 /* Number of kernels this handle has launched so far. */
 long long lassim_launch_count(const lassim_handle *h);

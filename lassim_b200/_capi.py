@@ -51,6 +51,8 @@ def load_library():
     lib.lassim_set_mask.argtypes = [H, c_ubyte_p]
     lib.lassim_set_tolerances.argtypes = [H, ctypes.c_double, ctypes.c_double,
                                           ctypes.c_longlong]
+    lib.lassim_set_method.argtypes = [H, ctypes.c_int]
+    lib.lassim_set_method.restype = ctypes.c_int
     lib.lassim_dim.argtypes = [H]
     lib.lassim_trajectories_per_candidate.argtypes = [H]
     lib.lassim_eval.argtypes = [H, ctypes.c_int, c_double_p, c_double_p,
@@ -66,6 +68,10 @@ def load_library():
                                         c_int_p]
     lib.lassim_last_end_states.argtypes = [H, ctypes.c_int, c_double_p]
     lib.lassim_last_traj_steps.argtypes = [H, ctypes.c_int, c_uint_p]
+    lib.lassim_flops_per_attempt.argtypes = [H]
+    lib.lassim_flops_per_attempt.restype = ctypes.c_longlong
+    lib.lassim_kernel_name.argtypes = [H]
+    lib.lassim_kernel_name.restype = ctypes.c_char_p
     lib.lassim_launch_count.argtypes = [H]
     lib.lassim_launch_count.restype = ctypes.c_longlong
     lib.lassim_last_kernel_ms.argtypes = [H, ctypes.POINTER(ctypes.c_float)]
@@ -105,6 +111,7 @@ class Engine:
             raise LassimError("lassim_create(device=%d) failed: %s" % (device, msg))
         self.device = int(device)
         self.n = self.T = 0
+        self.method = "dop853"
 
     # -- plumbing ----------------------------------------------------------
     def _check(self, rc, what):
@@ -158,6 +165,14 @@ class Engine:
     def set_tolerances(self, rtol=1.49012e-8, atol=1.49012e-8, max_steps=20000000):
         self._check(self._lib.lassim_set_tolerances(self._h, rtol, atol, int(max_steps)),
                     "lassim_set_tolerances")
+
+    def set_method(self, method="dop853"):
+        """'dop853' (Dormand-Prince 8(5,3), default) or 'dp45' (Dormand-Prince 5(4))."""
+        code = {"dp45": 0, "dop853": 1}.get(str(method).lower())
+        if code is None:
+            raise ValueError("unknown integrator %r (use 'dp45' or 'dop853')" % (method,))
+        self._check(self._lib.lassim_set_method(self._h, code), "lassim_set_method")
+        self.method = str(method).lower()
 
     @property
     def dim(self):
@@ -235,6 +250,14 @@ class Engine:
         self._check(self._lib.lassim_last_traj_steps(self._h, N, s.ctypes.data_as(c_uint_p)),
                     "lassim_last_traj_steps")
         return s
+
+    @property
+    def flops_per_attempt(self):
+        return int(self._lib.lassim_flops_per_attempt(self._h))
+
+    @property
+    def kernel_name(self):
+        return self._lib.lassim_kernel_name(self._h).decode()
 
     @property
     def launch_count(self):

@@ -1,18 +1,23 @@
 // Device side of the LASSIM cost evaluation for sm_100a.
 //
-// One lane group (G lanes of a warp, R genes per lane, G*R >= n) integrates one
-// (candidate, trajectory) pair with an FP64 adaptive Dormand-Prince 5(4) method
+// One lane group (L lanes, R genes per lane, L*R >= n) integrates one
+// (candidate, trajectory) pair with an FP64 adaptive explicit Runge-Kutta pair
 // whose error control mirrors the reference integrator's: error weight
 // rtol*|y| + atol, max-norm, rtol = atol = 1.49012e-8 by default (the reference
 // calls scipy.integrate.odeint = ODEPACK LSODA with its defaults,
 // source/core/functions/common_functions.pyx:86-90).
 //
-// Per lane, in registers: its R state entries, the seven stage derivatives,
-// lambda, vmax and its R dense rows of W.  The stage state is exchanged through
-// a double-buffered shared-memory line per group (one __syncwarp per RHS
-// evaluation, conflict-free 16-byte broadcast loads).  Groups pull work items
-// from a global atomic queue, so a warp keeps all of its groups busy although
-// step counts differ by orders of magnitude between trajectories.
+//   L <= 32  the group is a slice of a warp (Th2: 16 lanes, 2 groups per warp);
+//            the step loop is warp-uniform, groups of a warp run in lockstep
+//   L  > 32  the group is a whole CTA of L threads (n = 200: 128 lanes x 2 genes)
+//
+// Per lane, in registers: its R state entries, the stage derivatives, lambda,
+// vmax and its rows of W (dense for n <= 32, ELL or CSR beyond).  The stage
+// state is exchanged through a double-buffered shared-memory line per group
+// (one barrier per RHS evaluation, conflict-free 16-byte broadcast loads in the
+// dense case).  Groups pull work items from a global atomic queue, so all of
+// them stay busy although step counts differ by orders of magnitude between
+// trajectories.
 //
 // Fused reductions: the time-series cost (core_problem.py:89-90) is computed by
 // the group that integrated the time series; the knock-down cost
@@ -23,6 +28,8 @@
 #include <math_constants.h>
 #include <stdint.h>
 
+#include "rk_steppers.cuh"
+
 namespace lassim {
 
 struct DevProblem {
@@ -31,7 +38,9 @@ struct DevProblem {
     const double *y0;         // [n]
     const double *data;       // [T*n]
     const double *sigma2;     // [n]
-    const int *kidx;          // [n*n] index into the k part of x, or -1
+    const int *kidx;          // [n*n] index into the k part of x, or -1 (dense kernels)
+    const int *row_ptr;       // [n+1] CSR of the mask (sparse kernels)
+    const int *col_idx;       // [nnz]
     const double *pert;       // [n*(n+2)] or nullptr
     const int *traj_prefix;   // [K] rows whose lambda is already scaled
     const double *traj_tt;    // [K*2] start / end time (slot 0 unused)
@@ -57,58 +66,20 @@ struct DevBatch {
     const unsigned int *order;     // optional permutation of work items
 };
 
-// Dormand-Prince 5(4) tableau.
-#define DP_A21 (1.0 / 5.0)
-#define DP_A31 (3.0 / 40.0)
-#define DP_A32 (9.0 / 40.0)
-#define DP_A41 (44.0 / 45.0)
-#define DP_A42 (-56.0 / 15.0)
-#define DP_A43 (32.0 / 9.0)
-#define DP_A51 (19372.0 / 6561.0)
-#define DP_A52 (-25360.0 / 2187.0)
-#define DP_A53 (64448.0 / 6561.0)
-#define DP_A54 (-212.0 / 729.0)
-#define DP_A61 (9017.0 / 3168.0)
-#define DP_A62 (-355.0 / 33.0)
-#define DP_A63 (46732.0 / 5247.0)
-#define DP_A64 (49.0 / 176.0)
-#define DP_A65 (-5103.0 / 18656.0)
-#define DP_B1 (35.0 / 384.0)
-#define DP_B3 (500.0 / 1113.0)
-#define DP_B4 (125.0 / 192.0)
-#define DP_B5 (-2187.0 / 6784.0)
-#define DP_B6 (11.0 / 84.0)
-#define DP_E1 (71.0 / 57600.0)
-#define DP_E3 (-71.0 / 16695.0)
-#define DP_E4 (71.0 / 1920.0)
-#define DP_E5 (-17253.0 / 339200.0)
-#define DP_E6 (22.0 / 525.0)
-#define DP_E7 (-1.0 / 40.0)
+enum { kMethodDP45 = 0, kMethodDOP853 = 1 };
 
-// threads per CTA
-constexpr int threads_for(int G) { return G == 4 ? 256 : 128; }
+// threads per CTA for a group of L lanes
+constexpr int threads_for(int L) { return L > 32 ? L : (L == 4 ? 256 : 128); }
 
-template <int G>
-__device__ __forceinline__ double group_max(double v, unsigned gmask) {
-#pragma unroll
-    for (int o = G / 2; o > 0; o >>= 1)
-        v = fmax(v, __shfl_xor_sync(gmask, v, o, G));
-    return v;
-}
-
-template <int G>
-__device__ __forceinline__ double group_sum(double v, unsigned gmask) {
-#pragma unroll
-    for (int o = G / 2; o > 0; o >>= 1)
-        v += __shfl_xor_sync(gmask, v, o, G);
-    return v;
-}
+// doubles of shared memory in front of the groups' exchange lines:
+// 64 (2^(j/64) table) + 32 (reduction / broadcast scratch of a CTA-wide group)
+constexpr int kSmemHeader = 96;
 
 // 2^(j/64), j = 0..63, filled by the host when the engine is created.
 __constant__ double c_exp2_table[64];
 
-// With the fast logistic the rows of W are pre-scaled by -log2(e) at load, so
-// the mat-vec delivers t = -z*log2(e) directly.
+// With the fast logistic the weights are pre-scaled by -log2(e), so the
+// mat-vec delivers t = -z*log2(e) directly.
 constexpr double kSigScale = -1.4426950408889634074;
 
 // Exact-libm logistic with the reference's overflow behaviour: exp(-z) -> +inf
@@ -152,70 +123,262 @@ __device__ __forceinline__ double logistic_fast(double t, const double *tab) {
     return fma(r, fma(e0, e0, e0), r);
 }
 
-// sg = sigmoid(W ys) for this lane's genes; ys of the whole group goes through
-// buf.  With FAST the rows of W arrive pre-scaled by -log2(e).  NC = columns of W
-// actually used (n rounded up to 4).
-template <int G, int R, int NC, bool FAST, bool WHOLE_WARP>
-__device__ __forceinline__ void rhs_sigma(const double (&ys)[R], double (&sg)[R],
-                                          const double (&W)[R][NC], double *buf,
-                                          const double *tab, unsigned gmask,
-                                          int lg) {
+// ---------------------------------------------------------------- weights
+// Rows of W owned by one lane (genes g = lg*R + r).  `scale` is kSigScale on
+// the fast path, 1 otherwise.
+
+// Dense rows in registers, NC = n rounded up to 4 columns (n <= 32).
+template <int R, int NC>
+struct DenseW {
+    double w[R][NC];
+    __device__ __forceinline__ void clear() {
 #pragma unroll
-    for (int r = 0; r < R; ++r) buf[lg * R + r] = ys[r];
-    if (WHOLE_WARP) __syncwarp(); else __syncwarp(gmask);
-    double a0[R], a1[R], a2[R], a3[R];
+        for (int r = 0; r < R; ++r)
 #pragma unroll
-    for (int r = 0; r < R; ++r) { a0[r] = 0.0; a1[r] = 0.0; a2[r] = 0.0; a3[r] = 0.0; }
-#pragma unroll
-    for (int j = 0; j < NC; j += 4) {
-        const double2 v = *reinterpret_cast<const double2 *>(buf + j);
-        const double2 u = *reinterpret_cast<const double2 *>(buf + j + 2);
+            for (int j = 0; j < NC; ++j) w[r][j] = 0.0;
+    }
+    __device__ __forceinline__ void load(const DevProblem &P, const double *x, int lg,
+                                         const bool (&ok)[R], double scale) {
+        const int n = P.n;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            a0[r] = fma(W[r][j], v.x, a0[r]);
-            a1[r] = fma(W[r][j + 1], v.y, a1[r]);
-            a2[r] = fma(W[r][j + 2], u.x, a2[r]);
-            a3[r] = fma(W[r][j + 3], u.y, a3[r]);
+            const int g = lg * R + r;
+#pragma unroll
+            for (int j = 0; j < NC; ++j) {
+                double wv = 0.0;
+                if (ok[r] && j < n) {
+                    const int id = P.kidx[g * n + j];
+                    if (id >= 0) wv = x[2 * n + id];
+                }
+                w[r][j] = wv * scale;
+            }
         }
     }
+    __device__ __forceinline__ void matvec(const double *buf, double (&z)[R]) const {
+        double a0[R], a1[R], a2[R], a3[R];
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-        const double z = (a0[r] + a1[r]) + (a2[r] + a3[r]);
-        sg[r] = FAST ? logistic_fast(z, tab) : logistic_libm(z);
+        for (int r = 0; r < R; ++r) { a0[r] = 0.0; a1[r] = 0.0; a2[r] = 0.0; a3[r] = 0.0; }
+#pragma unroll
+        for (int j = 0; j < NC; j += 4) {
+            const double2 v = *reinterpret_cast<const double2 *>(buf + j);
+            const double2 u = *reinterpret_cast<const double2 *>(buf + j + 2);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                a0[r] = fma(w[r][j], v.x, a0[r]);
+                a1[r] = fma(w[r][j + 1], v.y, a1[r]);
+                a2[r] = fma(w[r][j + 2], u.x, a2[r]);
+                a3[r] = fma(w[r][j + 3], u.y, a3[r]);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) z[r] = (a0[r] + a1[r]) + (a2[r] + a3[r]);
     }
-}
+};
 
-template <int G, int R, int NC, bool FAST>
-__global__ void __launch_bounds__(threads_for(G))
+// ELL rows in registers: at most D regulators per gene.
+template <int R, int D>
+struct EllW {
+    double w[R][D];
+    int c[R][D];
+    __device__ __forceinline__ void clear() {
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int d = 0; d < D; ++d) { w[r][d] = 0.0; c[r][d] = 0; }
+    }
+    __device__ __forceinline__ void load(const DevProblem &P, const double *x, int lg,
+                                         const bool (&ok)[R], double scale) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int g = lg * R + r;
+            int beg = 0, end = 0;
+            if (ok[r]) { beg = P.row_ptr[g]; end = P.row_ptr[g + 1]; }
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                const int e = beg + d;
+                const bool in = e < end;
+                w[r][d] = in ? x[2 * P.n + e] * scale : 0.0;
+                c[r][d] = in ? P.col_idx[e] : 0;
+            }
+        }
+    }
+    __device__ __forceinline__ void matvec(const double *buf, double (&z)[R]) const {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+            for (int d = 0; d < D; d += 2) {
+                a0 = fma(w[r][d], buf[c[r][d]], a0);
+                if (d + 1 < D) a1 = fma(w[r][d + 1], buf[c[r][d + 1]], a1);
+            }
+            z[r] = a0 + a1;
+        }
+    }
+};
+
+// General rows: weights stay where they are (the k part of x is already in CSR
+// order), columns come from the problem's CSR.  Any in-degree, slower.
+template <int R>
+struct CsrW {
+    const double *xk;
+    const int *col;
+    int beg[R], end[R];
+    double scale_;
+    __device__ __forceinline__ void clear() {
+        xk = nullptr; col = nullptr; scale_ = 0.0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) { beg[r] = 0; end[r] = 0; }
+    }
+    __device__ __forceinline__ void load(const DevProblem &P, const double *x, int lg,
+                                         const bool (&ok)[R], double scale) {
+        xk = x + 2 * P.n;
+        col = P.col_idx;
+        scale_ = scale;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int g = lg * R + r;
+            beg[r] = ok[r] ? P.row_ptr[g] : 0;
+            end[r] = ok[r] ? P.row_ptr[g + 1] : 0;
+        }
+    }
+    __device__ __forceinline__ void matvec(const double *buf, double (&z)[R]) const {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            double a = 0.0;
+            for (int e = beg[r]; e < end[r]; ++e) a = fma(__ldg(xk + e), buf[__ldg(col + e)], a);
+            z[r] = a * scale_;
+        }
+    }
+};
+
+// ---------------------------------------------------------------- groups
+// Reductions / broadcasts over the L lanes of a group.  `red` is the CTA's 32
+// doubles of scratch (only touched when L > 32).
+template <int L>
+struct Grp {
+    static constexpr bool kWarp = (L <= 32);
+
+    // all lanes that run the step loop together (warp, or the CTA = the group)
+    __device__ static __forceinline__ void sync_domain() {
+        if constexpr (kWarp) __syncwarp(); else __syncthreads();
+    }
+    // the lanes of this group only (trajectory set-up and epilogue)
+    __device__ static __forceinline__ void sync_group(unsigned gmask) {
+        if constexpr (kWarp) __syncwarp(gmask); else __syncthreads();
+    }
+    // max of a non-negative float; the whole domain executes it
+    __device__ static __forceinline__ float max_domain(float v, double *red) {
+        if constexpr (kWarp) {
+#pragma unroll
+            for (int o = L / 2; o > 0; o >>= 1)
+                v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+            return v;
+        } else {
+            float *slot = reinterpret_cast<float *>(red);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+                v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+            if ((threadIdx.x & 31) == 0) slot[threadIdx.x >> 5] = v;
+            __syncthreads();
+            float m = 0.0f;
+#pragma unroll
+            for (int i = 0; i < L / 32; ++i) m = fmaxf(m, slot[i]);
+            __syncthreads();
+            return m;
+        }
+    }
+    __device__ static __forceinline__ double max_group(double v, unsigned gmask, double *red) {
+        if constexpr (kWarp) {
+#pragma unroll
+            for (int o = L / 2; o > 0; o >>= 1)
+                v = fmax(v, __shfl_xor_sync(gmask, v, o, L));
+            return v;
+        } else {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+                v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+            if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+            __syncthreads();
+            double m = red[0];
+#pragma unroll
+            for (int i = 1; i < L / 32; ++i) m = fmax(m, red[i]);
+            __syncthreads();
+            return m;
+        }
+    }
+    __device__ static __forceinline__ double sum_group(double v, unsigned gmask, double *red) {
+        if constexpr (kWarp) {
+#pragma unroll
+            for (int o = L / 2; o > 0; o >>= 1)
+                v += __shfl_xor_sync(gmask, v, o, L);
+            return v;
+        } else {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+                v += __shfl_xor_sync(0xffffffffu, v, o);
+            if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+            __syncthreads();
+            double m = 0.0;
+#pragma unroll
+            for (int i = 0; i < L / 32; ++i) m += red[i];
+            __syncthreads();
+            return m;
+        }
+    }
+    // value held by the group's lane 0 -> every lane
+    __device__ static __forceinline__ unsigned bcast(unsigned v, unsigned gmask, double *red) {
+        if constexpr (kWarp) {
+            return __shfl_sync(gmask, v, 0, L);
+        } else {
+            unsigned *slot = reinterpret_cast<unsigned *>(red);
+            if (threadIdx.x == 0) slot[0] = v;
+            __syncthreads();
+            const unsigned out = slot[0];
+            __syncthreads();
+            return out;
+        }
+    }
+};
+
+// ---------------------------------------------------------------- kernel
+template <int L, int R, class WT, int METHOD, bool FAST>
+__global__ void __launch_bounds__(threads_for(L))
 grn_cost_kernel(const DevProblem P, const DevBatch B) {
-    constexpr int NP = G * R;
+    constexpr int NP = L * R;
     constexpr int STRIDE = NP + 2;   // 16 B skew between groups: no bank conflicts
-    constexpr int GPW = 32 / G;
-    static_assert(NC <= NP && NC % 4 == 0, "NC must be a multiple of 4 within G*R");
+    constexpr bool kWarp = (L <= 32);
+    constexpr int LW = kWarp ? L : 32;               // lanes of the group inside one warp
+    using G = Grp<L>;
     extern __shared__ double smem[];
 
     const int lane = threadIdx.x & 31;
-    const int lg = lane % G;
-    const int gw = lane / G;
+    const int lg = kWarp ? (lane % LW) : (int)threadIdx.x;
+    const int gw = kWarp ? (lane / LW) : 0;
     const unsigned gmask =
-        (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (gw * G));
-    const int gid = (threadIdx.x >> 5) * GPW + gw;
+        (LW == 32) ? 0xffffffffu : (((1u << (LW & 31)) - 1u) << (gw * (LW & 31)));
+    const int gid = kWarp ? ((int)(threadIdx.x >> 5) * (32 / LW) + gw) : 0;
     double *tab = smem;
-    double *ybuf = smem + 64 + gid * (2 * STRIDE);
+    double *red = smem + 64;
+    double *ybuf = smem + kSmemHeader + gid * (2 * STRIDE);
     if (threadIdx.x < 64) tab[threadIdx.x] = c_exp2_table[threadIdx.x];
-    for (int i = lg; i < 2 * STRIDE; i += G) ybuf[i] = 0.0;
+    for (int i = lg; i < 2 * STRIDE; i += L) ybuf[i] = 0.0;
     __syncthreads();
 
     const int n = P.n;
     const int Kc = (B.mode == 0) ? P.K : 1;
     const unsigned total_work = (unsigned)B.N * (unsigned)Kc;
     const double rtol = P.rtol, atol = P.atol;
+    constexpr float kExpo = (METHOD == kMethodDOP853) ? -0.125f : -0.2f;
 
-    double y[R], k1[R], k2[R], k3[R], k4[R], k5[R], k6[R], k7[R], yn[R], ys[R];
-    double lam[R], vm[R], W[R][NC];
+    double y[R], k1[R], yn[R], kn[R], lam[R], vm[R];
+    WT wts;
+    wts.clear();                       // finite placeholders until work arrives
     bool gene_ok[R];
 #pragma unroll
-    for (int r = 0; r < R; ++r) gene_ok[r] = (lg * R + r) < n;
+    for (int r = 0; r < R; ++r) {
+        gene_ok[r] = (lg * R + r) < n;
+        y[r] = 0.0; k1[r] = 0.0; lam[r] = 0.0; vm[r] = 0.0;
+    }
 
     bool active = false, exhausted = false;
     int c = 0, k = 0, ti = 1, nt = 2, cur = 0, st = 0;
@@ -224,29 +387,28 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
     double t = 0.0, h = 0.0, tend = 0.0;
     const double *tl = P.times;
 
-    // LASSIM_SIG_G: only this group's lanes take part (trajectory set-up, which
-    // groups of one warp reach at different times).  LASSIM_SIG: the whole warp
-    // executes it together (the step loop is warp-uniform).
-#define LASSIM_SIG_G(in, out)                                                  \
-    do {                                                                       \
-        rhs_sigma<G, R, NC, FAST, false>(in, out, W, ybuf + cur * STRIDE, tab, \
-                                         gmask, lg);                           \
-        cur ^= 1;                                                              \
-    } while (0)
-#define LASSIM_SIG(in, out)                                                    \
-    do {                                                                       \
-        rhs_sigma<G, R, NC, FAST, true>(in, out, W, ybuf + cur * STRIDE, tab,  \
-                                        gmask, lg);                            \
-        cur ^= 1;                                                              \
-    } while (0)
+    // sg = sigmoid(W in): publish this lane's entries, barrier, mat-vec, logistic
+    auto sigma = [&](const double (&in)[R], double (&out)[R], bool whole_domain) {
+        double *buf = ybuf + cur * STRIDE;
+#pragma unroll
+        for (int r = 0; r < R; ++r) buf[lg * R + r] = in[r];
+        if (whole_domain) G::sync_domain(); else G::sync_group(gmask);
+        double z[R];
+        wts.matvec(buf, z);
+#pragma unroll
+        for (int r = 0; r < R; ++r) out[r] = FAST ? logistic_fast(z[r], tab) : logistic_libm(z[r]);
+        cur ^= 1;
+    };
+    auto sig_step = [&](const double (&in)[R], double (&out)[R]) { sigma(in, out, true); };
+    auto gmax_step = [&](float v) { return G::max_domain(v, red); };
 
     while (true) {
         if (!active && !exhausted) {
             unsigned w = 0;
             if (lg == 0) w = atomicAdd(B.work_counter, 1u);
-            w = __shfl_sync(gmask, w, 0, G);
+            w = G::bcast(w, gmask, red);
             if (w >= total_work) {
-                exhausted = true;
+                exhausted = true;      // registers are parked (see the epilogue)
             } else {
                 if (B.order != nullptr) w = B.order[w];
                 k = (int)(w / (unsigned)B.N);
@@ -264,16 +426,8 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                         vm[r] = x[n + g];
                         y[r] = P.y0[g];
                     }
-#pragma unroll
-                    for (int j = 0; j < NC; ++j) {
-                        double wv = 0.0;
-                        if (gene_ok[r] && j < n) {
-                            const int id = P.kidx[g * n + j];
-                            if (id >= 0) wv = x[2 * n + id];
-                        }
-                        W[r][j] = FAST ? wv * kSigScale : wv;
-                    }
                 }
+                wts.load(P, x, lg, gene_ok, FAST ? kSigScale : 1.0);
                 if (k == 0) { tl = P.times; nt = P.T; }
                 else { tl = P.traj_tt + 2 * k; nt = 2; }
                 t = tl[0];
@@ -288,8 +442,8 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                 }
                 // first derivative + starting step (Hairer/Norsett/Wanner II.4,
                 // max-norm variant)
-                double sg[R];
-                LASSIM_SIG_G(y, sg);
+                double sg[R], ys[R], k2[R];
+                sigma(y, sg, false);
 #pragma unroll
                 for (int r = 0; r < R; ++r) k1[r] = fma(vm[r], sg[r], -lam[r] * y[r]);
                 double d0 = 0.0, d1 = 0.0;
@@ -299,12 +453,12 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                     d0 = fmax(d0, fabs(y[r]) / sc);
                     d1 = fmax(d1, fabs(k1[r]) / sc);
                 }
-                d0 = group_max<G>(d0, gmask);
-                d1 = group_max<G>(d1, gmask);
+                d0 = G::max_group(d0, gmask, red);
+                d1 = G::max_group(d1, gmask, red);
                 const double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
 #pragma unroll
                 for (int r = 0; r < R; ++r) ys[r] = fma(h0, k1[r], y[r]);
-                LASSIM_SIG_G(ys, sg);
+                sigma(ys, sg, false);
 #pragma unroll
                 for (int r = 0; r < R; ++r) k2[r] = fma(vm[r], sg[r], -lam[r] * ys[r]);
                 double d2 = 0.0;
@@ -313,155 +467,40 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                     const double sc = fma(rtol, fabs(y[r]), atol);
                     d2 = fmax(d2, fabs(k2[r] - k1[r]) / sc);
                 }
-                d2 = group_max<G>(d2, gmask) / h0;
+                d2 = G::max_group(d2, gmask, red) / h0;
                 const double dm = fmax(d1, d2);
                 const double h1 = (dm <= 1e-15) ? fmax(1e-6, h0 * 1e-3)
-                                                : pow(0.01 / dm, 0.2);
+                                                : pow(0.01 / dm, (double)(-kExpo));
                 h = fmin(100.0 * h0, h1);
                 active = true;
                 if (nt < 2) ti = nt;   // a single sample time: nothing to integrate
             }
         }
-        if (!__any_sync(0xffffffffu, active)) break;
+        if constexpr (kWarp) {
+            if (!__any_sync(0xffffffffu, active)) break;
+        } else {
+            if (!active) break;        // one group per CTA: uniform
+        }
 
         {
             // ---------------------------------------------------- one attempt
-            // Executed by the whole warp together (no per-group branch): a
-            // group without a live trajectory computes on stale registers and
-            // its results are discarded.  This keeps __syncwarp and the
-            // shuffles full-mask and the groups of a warp in lockstep.
+            // Executed by the whole domain together (no per-group branch): a
+            // group without a live trajectory computes on parked registers and
+            // its results are discarded.  This keeps barriers and shuffles
+            // full-mask and the groups of a warp in lockstep.
             const bool live = active && ti < nt;
             double hs = h;
             bool hit = false;
             if (t + 1.01 * hs >= tend) { hs = tend - t; hit = true; }
-            // Stage s needs ys = y + hs*sum_j a_sj k_j with k_{s-1} = vm*sg + ly
-            // (ly = -lambda*ys_{s-1}) only just computed.  Everything except sg is
-            // known before the logistic finishes, so it is folded into q and the
-            // dependent chain from sg to the next stage state is ONE fma:
-            //   ys = fma(hs*a_last*vm, sg, q),  q = y + hs*sum_{j<s-1} + hs*a_last*ly
-            double sg[R], q[R], ly[R], cv[R];
-#pragma unroll
-            for (int r = 0; r < R; ++r) ys[r] = fma(hs * DP_A21, k1[r], y[r]);
-            {   // ---- stage 2 -> state of stage 3
-                const double hl = hs * DP_A32;
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    ly[r] = -lam[r] * ys[r];
-                    cv[r] = hl * vm[r];
-                    q[r] = fma(hl, ly[r], fma(hs * DP_A31, k1[r], y[r]));
-                }
-                LASSIM_SIG(ys, sg);
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    ys[r] = fma(cv[r], sg[r], q[r]);
-                    k2[r] = fma(vm[r], sg[r], ly[r]);
-                }
-            }
-            {   // ---- stage 3 -> state of stage 4
-                const double hl = hs * DP_A43;
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    ly[r] = -lam[r] * ys[r];
-                    cv[r] = hl * vm[r];
-                    q[r] = fma(hl, ly[r],
-                               fma(hs, fma(DP_A42, k2[r], DP_A41 * k1[r]), y[r]));
-                }
-                LASSIM_SIG(ys, sg);
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    ys[r] = fma(cv[r], sg[r], q[r]);
-                    k3[r] = fma(vm[r], sg[r], ly[r]);
-                }
-            }
-            {   // ---- stage 4 -> state of stage 5
-                const double hl = hs * DP_A54;
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    ly[r] = -lam[r] * ys[r];
-                    cv[r] = hl * vm[r];
-                    q[r] = fma(hl, ly[r],
-                               fma(hs, fma(DP_A53, k3[r],
-                                           fma(DP_A52, k2[r], DP_A51 * k1[r])), y[r]));
-                }
-                LASSIM_SIG(ys, sg);
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    ys[r] = fma(cv[r], sg[r], q[r]);
-                    k4[r] = fma(vm[r], sg[r], ly[r]);
-                }
-            }
-            {   // ---- stage 5 -> state of stage 6
-                const double hl = hs * DP_A65;
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    ly[r] = -lam[r] * ys[r];
-                    cv[r] = hl * vm[r];
-                    q[r] = fma(hl, ly[r],
-                               fma(hs, fma(DP_A64, k4[r],
-                                           fma(DP_A63, k3[r],
-                                               fma(DP_A62, k2[r], DP_A61 * k1[r]))), y[r]));
-                }
-                LASSIM_SIG(ys, sg);
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    ys[r] = fma(cv[r], sg[r], q[r]);
-                    k5[r] = fma(vm[r], sg[r], ly[r]);
-                }
-            }
-            {   // ---- stage 6 -> the 5th-order solution yn
-                const double hl = hs * DP_B6;
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    ly[r] = -lam[r] * ys[r];
-                    cv[r] = hl * vm[r];
-                    q[r] = fma(hl, ly[r],
-                               fma(hs, fma(DP_B5, k5[r],
-                                           fma(DP_B4, k4[r],
-                                               fma(DP_B3, k3[r], DP_B1 * k1[r]))), y[r]));
-                }
-                LASSIM_SIG(ys, sg);
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    yn[r] = fma(cv[r], sg[r], q[r]);
-                    k6[r] = fma(vm[r], sg[r], ly[r]);
-                }
-            }
-            // ---- stage 7 (FSAL) and the error estimate, again one fma after sg:
-            //   e = hs*(E1 k1 + E3 k3 + .. + E6 k6 + E7 k7),  k7 = vm*sg + ly
-            double isc[R], eq[R], ce[R];
-            {
-                const double hl = hs * DP_E7;
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    ly[r] = -lam[r] * yn[r];
-                    ce[r] = hl * vm[r];
-                    eq[r] = fma(hl, ly[r],
-                                hs * fma(DP_E6, k6[r],
-                                         fma(DP_E5, k5[r],
-                                             fma(DP_E4, k4[r],
-                                                 fma(DP_E3, k3[r], DP_E1 * k1[r])))));
-                    // the error weight only needs y and yn: off the critical path
-                    isc[r] = 1.0 / fma(rtol, fmax(fabs(y[r]), fabs(yn[r])), atol);
-                }
-                LASSIM_SIG(yn, sg);
-            }
-            double qd = 0.0;
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const double e = fma(ce[r], sg[r], eq[r]);
-                k7[r] = fma(vm[r], sg[r], ly[r]);
-                qd = fmax(qd, fabs(e) * isc[r]);      // fmax drops NaN: checked next
-                if (e != e) qd = CUDART_INF;
-            }
-            // max over the group as a float (IEEE order of non-negative floats);
-            // xor offsets below G stay inside the group, so full-mask shuffles do
-            float qf = (qd <= 3.0e38) ? (float)qd : CUDART_INF_F;
-#pragma unroll
-            for (int o = G / 2; o > 0; o >>= 1)
-                qf = fmaxf(qf, __shfl_xor_sync(0xffffffffu, qf, o));
+
+            float qf;
+            if constexpr (METHOD == kMethodDOP853)
+                qf = dop853_attempt<R>(sig_step, gmax_step, lam, vm, y, k1, hs, rtol, atol, yn, kn);
+            else
+                qf = dp45_attempt<R>(sig_step, gmax_step, lam, vm, y, k1, hs, rtol, atol, yn, kn);
 
             const float qc = fminf(fmaxf(qf, 1e-30f), 3.0e38f);
-            const float fac0 = 0.9f * exp2f(-0.2f * __log2f(qc));
+            const float fac0 = 0.9f * exp2f(kExpo * __log2f(qc));
             const bool accept = qf <= 1.0f;
             bool failed = false;
             if (live) {
@@ -469,7 +508,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                     ++nacc;
                     t = hit ? tend : t + hs;
 #pragma unroll
-                    for (int r = 0; r < R; ++r) { y[r] = yn[r]; k1[r] = k7[r]; }
+                    for (int r = 0; r < R; ++r) { y[r] = yn[r]; k1[r] = kn[r]; }
                     float fac = fminf(10.0f, fmaxf(0.2f, fac0));
                     if (rejected) fac = fminf(fac, 1.0f);
                     rejected = false;
@@ -536,7 +575,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                         }
                     }
                 }
-                part = group_sum<G>(part, gmask);
+                part = G::sum_group(part, gmask, red);
                 if (lg == 0) B.cost_main[c] = part;
             } else {
                 double *Ec = B.E + ((size_t)c * P.K + k) * n;
@@ -544,22 +583,28 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                 for (int r = 0; r < R; ++r)
                     if (gene_ok[r]) Ec[lg * R + r] = y[r];
             }
+            constexpr unsigned long long kRhsPerAttempt = (METHOD == kMethodDOP853) ? 12ull : 6ull;
             if (lg == 0) {
                 B.traj_steps[(size_t)c * P.K + k] = nacc + nrej;
                 atomicAdd(&B.counters[(size_t)c * 3 + 0], (unsigned long long)nacc);
                 atomicAdd(&B.counters[(size_t)c * 3 + 1], (unsigned long long)nrej);
                 atomicAdd(&B.counters[(size_t)c * 3 + 2],
-                          (unsigned long long)(6u * (nacc + nrej) + 2u));
+                          kRhsPerAttempt * (unsigned long long)(nacc + nrej) + 2ull);
                 if (st) atomicOr(&B.status[c], st);
             }
             active = false;
+            // park: until new work arrives this group only goes through the
+            // motions of the step loop with its warp; keep its registers finite
+#pragma unroll
+            for (int r = 0; r < R; ++r) { y[r] = 0.0; k1[r] = 0.0; }
+            h = 0.0; t = 0.0; tend = 0.0;
             if (B.mode == 0) {
                 __threadfence();
-                __syncwarp(gmask);
-                int old = 0;
-                if (lg == 0) old = atomicAdd(&B.done[c], 1);
-                old = __shfl_sync(gmask, old, 0, G);
-                if (old == Kc - 1) {
+                G::sync_group(gmask);
+                unsigned old = 0;
+                if (lg == 0) old = (unsigned)atomicAdd(&B.done[c], 1);
+                old = G::bcast(old, gmask, red);
+                if ((int)old == Kc - 1) {
                     // last trajectory of candidate c: knock-down cost + total
                     __threadfence();
                     double pc = 0.0;
@@ -581,8 +626,8 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                                 }
                             }
                         }
-                        rmax = group_max<G>(rmax, gmask);
-                        pp = group_sum<G>(pp, gmask);
+                        rmax = G::max_group(rmax, gmask, red);
+                        pp = G::sum_group(pp, gmask, red);
                         double rp = 0.0, rr2 = 0.0;
                         const double inv = (rmax > 0.0) ? 1.0 / rmax : 0.0;
                         for (int i = 0; i < n; ++i) {
@@ -601,8 +646,8 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                                 }
                             }
                         }
-                        rp = group_sum<G>(rp, gmask);
-                        rr2 = group_sum<G>(rr2, gmask);
+                        rp = G::sum_group(rp, gmask, red);
+                        rr2 = G::sum_group(rr2, gmask, red);
                         pc = (rmax > 0.0) ? pp - rp * rp / rr2 : pp;
                     }
                     if (lg == 0) {
@@ -614,8 +659,6 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
             }
         }
     }
-#undef LASSIM_SIG
-#undef LASSIM_SIG_G
 }
 
 // Register-resident DFMA throughput probe (roofline denominator).

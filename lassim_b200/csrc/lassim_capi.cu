@@ -41,12 +41,13 @@ struct lassim_handle {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
-    std::string err;
+    std::string err, kernel_name;
     long long launches = 0;
 
     // problem (host copies)
     bool has_problem = false;
-    int n = 0, T = 0, K = 1, U = 0, nnz = 0, dim = 0;
+    int n = 0, T = 0, K = 1, U = 0, nnz = 0, dim = 0, max_deg = 0;
+    int method = 1;   // kMethodDP45 = 0 / kMethodDOP853 = 1 (default)
     std::vector<double> pert_h;
     double pert_factor = 0.0;
     double rtol = 1.49012e-8, atol = 1.49012e-8;
@@ -54,7 +55,7 @@ struct lassim_handle {
 
     // problem (device)
     DevBuf<double> d_times, d_y0, d_data, d_sigma2, d_pert, d_traj_tt;
-    DevBuf<int> d_kidx, d_traj_prefix, d_knock_ctrl;
+    DevBuf<int> d_kidx, d_row_ptr, d_col_idx, d_traj_prefix, d_knock_ctrl;
 
     // scratch
     DevBuf<double> d_X, d_cost, d_cost_main, d_pert_cost, d_Y, d_E, d_probe;
@@ -95,14 +96,27 @@ int upload(lassim_handle *h, DevBuf<T> &buf, const T *src, size_t count) {
 
 int upload_mask(lassim_handle *h, const unsigned char *mask) {
     const int n = h->n;
-    std::vector<int> kidx((size_t)n * n);
-    int cnt = 0;
-    for (int i = 0; i < n * n; ++i) kidx[i] = mask[i] ? cnt++ : -1;
+    std::vector<int> kidx((size_t)n * n), row_ptr(n + 1, 0), col_idx;
+    int cnt = 0, max_deg = 0;
+    for (int i = 0; i < n; ++i) {
+        for (int j = 0; j < n; ++j) {
+            const bool on = mask[(size_t)i * n + j] != 0;
+            kidx[(size_t)i * n + j] = on ? cnt++ : -1;
+            if (on) col_idx.push_back(j);
+        }
+        row_ptr[i + 1] = cnt;
+        if (row_ptr[i + 1] - row_ptr[i] > max_deg) max_deg = row_ptr[i + 1] - row_ptr[i];
+    }
     h->nnz = cnt;
     h->dim = 2 * n + cnt;
-    int rc = upload(h, h->d_kidx, kidx.data(), kidx.size());
-    if (rc) return rc;
-    CU(cudaStreamSynchronize(h->stream));   // kidx is a local
+    h->max_deg = max_deg;
+    int rc;
+    if (n <= 32) {   // the dense kernels read the n*n index map
+        if ((rc = upload(h, h->d_kidx, kidx.data(), kidx.size()))) return rc;
+    }
+    if ((rc = upload(h, h->d_row_ptr, row_ptr.data(), row_ptr.size()))) return rc;
+    if ((rc = upload(h, h->d_col_idx, col_idx.data(), col_idx.size()))) return rc;
+    CU(cudaStreamSynchronize(h->stream));   // the vectors are locals
     return LASSIM_OK;
 }
 
@@ -123,58 +137,77 @@ typedef void (*kernel_fn)(const DevProblem, const DevBatch);
 
 struct KernelChoice {
     kernel_fn fn;
-    int G, R;
-    bool fast;
+    int L, R;          // lanes per group, genes per lane
+    const char *name;
 };
 
-// dynamic shared memory of one CTA: the 2^(j/64) table + the groups'
-// double-buffered exchange lines
+// dynamic shared memory of one CTA: header (2^(j/64) table, reduction scratch)
+// + the groups' double-buffered exchange lines
 size_t smem_bytes(const KernelChoice &kc) {
-    const int groups_per_cta = threads_for(kc.G) / kc.G;
-    return (64 + (size_t)groups_per_cta * 2 * (kc.G * kc.R + 2)) * sizeof(double);
+    const int groups_per_cta = threads_for(kc.L) / kc.L;
+    return ((size_t)kSmemHeader + (size_t)groups_per_cta * 2 * (kc.L * kc.R + 2)) * sizeof(double);
 }
 
-template <int G, int R, bool FAST>
-kernel_fn pick_columns(int n) {
-    constexpr int NP = G * R;
-    const int nc = (n + 3) & ~3;
-    if (nc <= 4 && 4 <= NP) return grn_cost_kernel<G, R, 4 <= NP ? 4 : NP, FAST>;
-    if (nc <= 8 && 8 <= NP) return grn_cost_kernel<G, R, 8 <= NP ? 8 : NP, FAST>;
-    if (nc <= 12 && 12 <= NP) return grn_cost_kernel<G, R, 12 <= NP ? 12 : NP, FAST>;
-    if (nc <= 16 && 16 <= NP) return grn_cost_kernel<G, R, 16 <= NP ? 16 : NP, FAST>;
-    if (nc <= 24 && 24 <= NP) return grn_cost_kernel<G, R, 24 <= NP ? 24 : NP, FAST>;
-    return grn_cost_kernel<G, R, NP, FAST>;
+template <int L, int NC>
+kernel_fn dense_kernel(int method, bool fast) {
+    if (method == kMethodDOP853) return grn_cost_kernel<L, 1, DenseW<1, NC>, kMethodDOP853, true>;
+    if (!fast) return grn_cost_kernel<L, 1, DenseW<1, NC>, kMethodDP45, false>;
+    return grn_cost_kernel<L, 1, DenseW<1, NC>, kMethodDP45, true>;
 }
 
-// Which lane-group shape serves a state size.  LASSIM_GROUP=G overrides the
-// choice between shapes that both fit and LASSIM_EXACT_MATH=1 selects libm
-// exp + IEEE division instead of the exp2/Newton logistic (diagnostics).
-bool choose_kernel(int n, KernelChoice *out) {
+template <int L>
+kernel_fn sparse_kernel(int method, int max_deg) {
+    if (max_deg <= 8) {
+        if (method == kMethodDOP853) return grn_cost_kernel<L, 2, EllW<2, 8>, kMethodDOP853, true>;
+        return grn_cost_kernel<L, 2, EllW<2, 8>, kMethodDP45, true>;
+    }
+    if (method == kMethodDOP853) return grn_cost_kernel<L, 2, CsrW<2>, kMethodDOP853, true>;
+    return grn_cost_kernel<L, 2, CsrW<2>, kMethodDP45, true>;
+}
+
+// Which kernel serves a problem.  n <= 16: 16-lane groups, dense rows; n <= 32:
+// one warp, dense rows; beyond: two genes per lane, ELL rows (in-degree <= 8) or
+// CSR, one warp up to n = 64, a 128-thread CTA up to 256, 512 threads up to 1024.
+// LASSIM_GROUP=4 selects the 4-lane x 3-gene throughput shape for n <= 12 and
+// LASSIM_EXACT_MATH=1 libm exp + IEEE division instead of the fast logistic
+// (both diagnostics, DP45 only).
+bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
+    const int n = h->n, method = h->method;
     const char *env = getenv("LASSIM_GROUP");
     const int want = env ? atoi(env) : 0;
     const char *ex = getenv("LASSIM_EXACT_MATH");
     const bool fast = !(ex && atoi(ex) != 0);
-    if (n <= 12 && want == 4) {   // four lanes x three genes: throughput shape
-        *out = {pick_columns<4, 3, true>(n), 4, 3, true};
+    const int nc = (n + 3) & ~3;
+    if (n <= 12 && want == 4 && method == kMethodDP45) {
+        *out = {grn_cost_kernel<4, 3, DenseW<3, 12>, kMethodDP45, true>, 4, 3, "dense 4x3"};
         return true;
     }
     if (n <= 16) {
-        *out = {fast ? pick_columns<16, 1, true>(n) : pick_columns<16, 1, false>(n), 16, 1, fast};
+        kernel_fn fn = nc <= 4 ? dense_kernel<16, 4>(method, fast)
+                     : nc <= 8 ? dense_kernel<16, 8>(method, fast)
+                     : nc <= 12 ? dense_kernel<16, 12>(method, fast)
+                                : dense_kernel<16, 16>(method, fast);
+        *out = {fn, 16, 1, "dense 16x1"};
         return true;
     }
     if (n <= 32) {
-        *out = {fast ? pick_columns<32, 1, true>(n) : pick_columns<32, 1, false>(n), 32, 1, fast};
+        kernel_fn fn = nc <= 24 ? dense_kernel<32, 24>(method, fast)
+                                : dense_kernel<32, 32>(method, fast);
+        *out = {fn, 32, 1, "dense 32x1"};
         return true;
     }
+    if (n <= 64) { *out = {sparse_kernel<32>(method, h->max_deg), 32, 2, "sparse 32x2"}; return true; }
+    if (n <= 256) { *out = {sparse_kernel<128>(method, h->max_deg), 128, 2, "sparse 128x2"}; return true; }
+    if (n <= 1024) { *out = {sparse_kernel<512>(method, h->max_deg), 512, 2, "sparse 512x2"}; return true; }
     return false;
 }
 
 int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
                 cudaStream_t s) {
     KernelChoice kc;
-    if (!choose_kernel(h->n, &kc))
+    if (!choose_kernel(h, &kc))
         return fail(h, LASSIM_E_UNSUPPORTED,
-                    "state size n=%d is outside the kernels built (n <= 32)", h->n);
+                    "state size n=%d is outside the kernels built (n <= 1024)", h->n);
     const int K = h->K, n = h->n;
     const ZeroLayout z = zero_layout(N);
     CU(h->d_zero.reserve(z.bytes));
@@ -194,6 +227,7 @@ int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
     P.n = n; P.T = h->T; P.K = K; P.U = h->U; P.dim = h->dim; P.nnz = h->nnz;
     P.times = h->d_times.p; P.y0 = h->d_y0.p; P.data = h->d_data.p;
     P.sigma2 = h->d_sigma2.p; P.kidx = h->d_kidx.p;
+    P.row_ptr = h->d_row_ptr.p; P.col_idx = h->d_col_idx.p;
     P.pert = (K > 1) ? h->d_pert.p : nullptr;
     P.traj_prefix = h->d_traj_prefix.p; P.traj_tt = h->d_traj_tt.p;
     P.knock_ctrl = h->d_knock_ctrl.p;
@@ -209,12 +243,12 @@ int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
     B.counters = reinterpret_cast<unsigned long long *>(h->d_zero.p + z.off_counters);
     B.Y = dY; B.E = h->d_E.p; B.traj_steps = h->d_steps.p; B.order = nullptr;
 
-    const int groups_per_cta = threads_for(kc.G) / kc.G;
+    const int groups_per_cta = threads_for(kc.L) / kc.L;
     const size_t smem = smem_bytes(kc);
     CU(cudaFuncSetAttribute((const void *)kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
                             (int)smem));
     int per_sm = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kc.fn, threads_for(kc.G), smem));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kc.fn, threads_for(kc.L), smem));
     if (per_sm < 1) per_sm = 1;
     const long long work = (long long)N * (mode == 0 ? K : 1);
     long long blocks = (work + groups_per_cta - 1) / groups_per_cta;
@@ -223,7 +257,7 @@ int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
     if (blocks < 1) blocks = 1;
 
     CU(cudaEventRecord(h->ev0, s));
-    kc.fn<<<(unsigned)blocks, threads_for(kc.G), smem, s>>>(P, B);
+    kc.fn<<<(unsigned)blocks, threads_for(kc.L), smem, s>>>(P, B);
     CU(cudaGetLastError());
     CU(cudaEventRecord(h->ev1, s));
     h->timed = true;
@@ -289,6 +323,7 @@ int lassim_destroy(lassim_handle *h) {
     cudaStreamSynchronize(h->stream);
     h->d_times.release(); h->d_y0.release(); h->d_data.release(); h->d_sigma2.release();
     h->d_pert.release(); h->d_traj_tt.release(); h->d_kidx.release();
+    h->d_row_ptr.release(); h->d_col_idx.release();
     h->d_traj_prefix.release(); h->d_knock_ctrl.release();
     h->d_X.release(); h->d_cost.release(); h->d_cost_main.release();
     h->d_pert_cost.release(); h->d_Y.release(); h->d_E.release(); h->d_probe.release();
@@ -306,10 +341,9 @@ int lassim_set_problem(lassim_handle *h, int n, int T, const double *times,
     if (!h) return LASSIM_E_INVALID;
     if (n < 1 || T < 1 || !times || !y0 || !data || !sigma || !mask)
         return fail(h, LASSIM_E_INVALID, "set_problem: n=%d T=%d or a NULL array", n, T);
-    KernelChoice kc;
-    if (!choose_kernel(n, &kc))
+    if (n > 1024)
         return fail(h, LASSIM_E_UNSUPPORTED,
-                    "state size n=%d is outside the kernels built (n <= 32)", n);
+                    "state size n=%d is outside the kernels built (n <= 1024)", n);
     for (int i = 1; i < T; ++i)
         if (!(times[i] >= times[i - 1]))
             return fail(h, LASSIM_E_UNSUPPORTED,
@@ -391,6 +425,32 @@ int lassim_set_tolerances(lassim_handle *h, double rtol, double atol, long long 
                     rtol, atol, max_steps);
     h->rtol = rtol; h->atol = atol; h->max_steps = max_steps;
     return LASSIM_OK;
+}
+
+int lassim_set_method(lassim_handle *h, int method) {
+    if (!h) return LASSIM_E_INVALID;
+    if (method != kMethodDP45 && method != kMethodDOP853)
+        return fail(h, LASSIM_E_INVALID, "unknown integrator %d (0 = DP5(4), 1 = DP8(5,3))", method);
+    h->method = method;
+    return LASSIM_OK;
+}
+
+long long lassim_flops_per_attempt(const lassim_handle *h) {
+    if (!h || !h->has_problem) return -1;
+    // F_rhs = 2*nnz + 5*n per RHS evaluation.  5(4): 6 RHS + 42 + 3
+    // FMAs/ops per gene = 12*nnz + 90*n.  8(5,3): 12 RHS + 74 tableau FMAs (50 in A,
+    // 8 each in b, e5, e3) + 4 = 24*nnz + 212*n.
+    const long long nnz = h->nnz, n = h->n;
+    return h->method == kMethodDOP853 ? 24 * nnz + 212 * n : 12 * nnz + 90 * n;
+}
+
+const char *lassim_kernel_name(lassim_handle *h) {
+    if (!h || !h->has_problem) return "";
+    KernelChoice kc;
+    if (!choose_kernel(h, &kc)) return "";
+    h->kernel_name = std::string("grn_cost_kernel<") + kc.name +
+                     (h->method == kMethodDOP853 ? ", dop853>" : ", dp45>");
+    return h->kernel_name.c_str();
 }
 
 int lassim_dim(const lassim_handle *h) { return (h && h->has_problem) ? h->dim : -1; }
@@ -617,9 +677,9 @@ extern "C" int lassim_eval_device_noalloc(lassim_handle *h, int N, const double 
     }
     unsigned char *base = g_noalloc_addr[h->device];
     KernelChoice kc;
-    if (!choose_kernel(n, &kc))
+    if (!choose_kernel(h, &kc))
         return fail(h, LASSIM_E_UNSUPPORTED,
-                    "state size n=%d is outside the kernels built (n <= 32)", n);
+                    "state size n=%d is outside the kernels built (n <= 1024)", n);
     cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
     // the array keeps whatever the previous call left: clear what must be zero
     CU(cudaMemsetAsync(base, 0, L.zero_bytes, s));
@@ -628,6 +688,7 @@ extern "C" int lassim_eval_device_noalloc(lassim_handle *h, int N, const double 
     P.n = n; P.T = T; P.K = K; P.U = h->U; P.dim = h->dim; P.nnz = h->nnz;
     P.times = h->d_times.p; P.y0 = h->d_y0.p; P.data = h->d_data.p;
     P.sigma2 = h->d_sigma2.p; P.kidx = h->d_kidx.p;
+    P.row_ptr = h->d_row_ptr.p; P.col_idx = h->d_col_idx.p;
     P.pert = (K > 1) ? h->d_pert.p : nullptr;
     P.traj_prefix = h->d_traj_prefix.p; P.traj_tt = h->d_traj_tt.p;
     P.knock_ctrl = h->d_knock_ctrl.p;
@@ -648,18 +709,18 @@ extern "C" int lassim_eval_device_noalloc(lassim_handle *h, int N, const double 
     B.E = reinterpret_cast<double *>(base + L.off_E);
     B.order = nullptr;
 
-    const int groups_per_cta = threads_for(kc.G) / kc.G;
+    const int groups_per_cta = threads_for(kc.L) / kc.L;
     const size_t smem = smem_bytes(kc);
     CU(cudaFuncSetAttribute((const void *)kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
                             (int)smem));
     int per_sm = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kc.fn, threads_for(kc.G), smem));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kc.fn, threads_for(kc.L), smem));
     if (per_sm < 1) per_sm = 1;
     const long long work = (long long)N * K;
     long long blocks = (work + groups_per_cta - 1) / groups_per_cta;
     const long long resident = (long long)h->sm_count * per_sm;
     if (blocks > resident) blocks = resident;
-    kc.fn<<<(unsigned)blocks, threads_for(kc.G), smem, s>>>(P, B);
+    kc.fn<<<(unsigned)blocks, threads_for(kc.L), smem, s>>>(P, B);
     CU(cudaGetLastError());
     h->launches += 1;
     return LASSIM_OK;

@@ -1,0 +1,168 @@
+"""Generates lassim_b200/csrc/rk_steppers.cuh: one fully unrolled step attempt
+per explicit Runge-Kutta pair (Dormand-Prince 5(4) and Dormand-Prince 8(5,3)).
+
+Why generated: the hot loop wants every coefficient as an immediate, zero
+coefficients skipped, and the terms of the next stage state that do not depend
+on the logistic being evaluated folded in advance (so that the dependent chain
+from the logistic to the next stage state is a single FMA).  Writing that out by
+hand for the 12-stage tableau invites typos; the 8(5,3) coefficients are taken
+from SciPy's table (scipy.integrate._ivp.dop853_coefficients, which reproduces
+Hairer's dop853.f) when the header is generated.
+
+Usage: python tools/gen_rk_steppers.py   (rewrites the header; commit it)
+"""
+import os
+from fractions import Fraction
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+OUT = os.path.join(os.path.dirname(HERE), "lassim_b200", "csrc", "rk_steppers.cuh")
+
+
+def lit(v):
+    v = float(v)
+    s = repr(v)
+    if "e" not in s and "." not in s and "inf" not in s:
+        s += ".0"
+    return s
+
+
+def dp45():
+    F = Fraction
+    A = [[], [F(1, 5)], [F(3, 40), F(9, 40)], [F(44, 45), F(-56, 15), F(32, 9)],
+         [F(19372, 6561), F(-25360, 2187), F(64448, 6561), F(-212, 729)],
+         [F(9017, 3168), F(-355, 33), F(46732, 5247), F(49, 176), F(-5103, 18656)]]
+    B = [F(35, 384), 0, F(500, 1113), F(125, 192), F(-2187, 6784), F(11, 84)]
+    E = [F(71, 57600), 0, F(-71, 16695), F(71, 1920), F(-17253, 339200), F(22, 525), F(-1, 40)]
+    A = [[float(x) for x in row] for row in A]
+    return dict(name="dp45", S=6, order=5, A=A, B=[float(b) for b in B],
+                E=[[float(e) for e in E]])
+
+
+def dop853():
+    from scipy.integrate._ivp import dop853_coefficients as dc
+    S = 12
+    A = [[float(dc.A[s, j]) for j in range(s)] for s in range(S)]
+    return dict(name="dop853", S=S, order=8, A=A, B=[float(b) for b in dc.B],
+                E=[[float(e) for e in dc.E5], [float(e) for e in dc.E3]])
+
+
+def weighted_sum(coefs, names, indent):
+    """Nested-fma expression for sum_j coefs[j] * names[j][r] (zeros skipped)."""
+    terms = [(c, n) for c, n in zip(coefs, names) if c != 0.0]
+    if not terms:
+        return "0.0"
+    expr = "%s * %s[r]" % (lit(terms[0][0]), terms[0][1])
+    for c, n in terms[1:]:
+        expr = "fma(%s, %s[r], %s)" % (lit(c), n, expr)
+    return expr
+
+
+def emit(tb):
+    S, A, B, E = tb["S"], tb["A"], tb["B"], tb["E"]
+    name = tb["name"]
+    K = ["k%d" % (i + 1) for i in range(S + 1)]          # k1 .. k_{S+1}
+    L = []
+    w = L.append
+    w("// %s: one step attempt of size hs from (y, k1 = f(y))." % name)
+    w("//   sig(ys, sg)  evaluates the logistic terms sg = sigmoid(W ys) for this lane's genes")
+    w("//   gmax(x)      max of a non-negative float over the lanes of the group")
+    w("// Outputs: yn (the order-%d solution), kn = f(yn); returns the group's error measure"
+      % tb["order"])
+    w("// (accept if <= 1), +inf when anything was non-finite.")
+    w("template <int R, class Sig, class GMax>")
+    w("__device__ __forceinline__ float %s_attempt(Sig &&sig, GMax &&gmax," % name)
+    w("        const double (&lam)[R], const double (&vm)[R], const double (&y)[R],")
+    w("        const double (&k1)[R], const double hs, const double rtol, const double atol,")
+    w("        double (&yn)[R], double (&kn)[R]) {")
+    decl = ", ".join("%s[R]" % k for k in K[1:S])
+    w("    double %s;" % decl)
+    w("    double ys[R], sg[R], q[R], ly[R], cv[R];")
+    w("#pragma unroll")
+    w("    for (int r = 0; r < R; ++r) ys[r] = fma(hs * %s, k1[r], y[r]);" % lit(A[1][0]))
+    for s in range(2, S + 1):
+        row = A[s] if s < S else B
+        last = row[s - 1]
+        target = "ys" if s < S else "yn"
+        w("    {   // sigma at stage %d's state -> %s, %s" % (s, K[s - 1], "state of stage %d" % (s + 1) if s < S else "yn"))
+        w("        const double hl = hs * %s;" % lit(last))
+        w("#pragma unroll")
+        w("        for (int r = 0; r < R; ++r) {")
+        w("            ly[r] = -lam[r] * ys[r];")
+        w("            cv[r] = hl * vm[r];")
+        w("            q[r] = fma(hl, ly[r], fma(hs, %s, y[r]));" % weighted_sum(row[:s - 1], K[:s - 1], 16))
+        w("        }")
+        w("        sig(ys, sg);")
+        w("#pragma unroll")
+        w("        for (int r = 0; r < R; ++r) {")
+        w("            %s[r] = fma(cv[r], sg[r], q[r]);" % target)
+        w("            %s[r] = fma(vm[r], sg[r], ly[r]);" % K[s - 1])
+        w("        }")
+        w("    }")
+    # last evaluation f(yn) and the error estimates
+    nE = len(E)
+    w("    // f(yn) (first stage of the next step) and the error estimate%s" % ("s" if nE > 1 else ""))
+    w("    double isc[R];")
+    for m in range(nE):
+        w("    double eq%d[R], ce%d[R];" % (m, m))
+    w("#pragma unroll")
+    w("    for (int r = 0; r < R; ++r) {")
+    w("        ly[r] = -lam[r] * yn[r];")
+    for m in range(nE):
+        e_last = E[m][S]
+        base = "hs * (%s)" % weighted_sum(E[m][:S], K[:S], 8)
+        if e_last != 0.0:
+            w("        ce%d[r] = (hs * %s) * vm[r];" % (m, lit(e_last)))
+            w("        eq%d[r] = fma(hs * %s, ly[r], %s);" % (m, lit(e_last), base))
+        else:
+            w("        ce%d[r] = 0.0;" % m)
+            w("        eq%d[r] = %s;" % (m, base))
+    w("        // error weight rtol*max(|y|,|yn|) + atol: needs y and yn only, off the critical path")
+    w("        isc[r] = 1.0 / fma(rtol, fmax(fabs(y[r]), fabs(yn[r])), atol);")
+    w("    }")
+    w("    sig(yn, sg);")
+    for m in range(nE):
+        w("    double qd%d = 0.0;" % m)
+    w("#pragma unroll")
+    w("    for (int r = 0; r < R; ++r) {")
+    w("        kn[r] = fma(vm[r], sg[r], ly[r]);")
+    for m in range(nE):
+        if E[m][S] != 0.0:
+            w("        const double e%d = fma(ce%d[r], sg[r], eq%d[r]);" % (m, m, m))
+        else:
+            w("        const double e%d = eq%d[r];" % (m, m))
+        w("        qd%d = fmax(qd%d, fabs(e%d) * isc[r]);      // fmax drops NaN: checked next" % (m, m, m))
+        w("        if (e%d != e%d) qd%d = CUDART_INF;" % (m, m, m))
+    w("    }")
+    for m in range(nE):
+        w("    const float n%d = gmax((qd%d <= 3.0e38) ? (float)qd%d : CUDART_INF_F);" % (m, m, m))
+    if nE == 1:
+        w("    return n0;")
+    else:
+        w("    // Hairer's 8(5,3) measure err5^2 / sqrt(err5^2 + 0.01 err3^2), in the max-norm")
+        w("    if (!(n0 < 1.0e18f) || !(n1 < 1.0e18f)) return CUDART_INF_F;")
+        w("    const float den = fmaf(n0, n0, 0.01f * n1 * n1);")
+        w("    return den > 0.0f ? n0 * n0 * rsqrtf(den) : 0.0f;")
+    w("}")
+    w("")
+    return "\n".join(L)
+
+
+def main():
+    parts = ["// GENERATED by tools/gen_rk_steppers.py - do not edit by hand.",
+             "// Fully unrolled step attempts of the explicit Runge-Kutta pairs used by",
+             "// grn_cost_kernel.  Every stage state after the second is formed as",
+             "//   ys = fma(hs*a_last*vm, sg, q),  q = y + hs*sum_{older k} + hs*a_last*(-lambda*ys_prev)",
+             "// so only one FMA separates the logistic sg from the next stage state.",
+             "#pragma once", "#include <math_constants.h>", "", "namespace lassim {", ""]
+    parts.append(emit(dp45()))
+    parts.append(emit(dop853()))
+    parts.append("}  // namespace lassim\n")
+    with open(OUT, "w") as fh:
+        fh.write("\n".join(parts))
+    print("wrote", OUT)
+
+
+if __name__ == "__main__":
+    main()

@@ -22,6 +22,7 @@ def log(*a):
 
 
 eng = Engine(0)
+eng.set_method(os.environ.get('LASSIM_METHOD', 'dop853'))
 log("fp64 probe TFLOP/s:", eng.fp64_peak_tflops(200000))
 eng.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"], p["pert"], 0.5)
 log("dim", eng.dim, "K", eng.trajectories_per_candidate)

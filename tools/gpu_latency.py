@@ -9,6 +9,7 @@ gold = os.path.join(REPO, "tests", "golden")
 p = dict(np.load(os.path.join(gold, "th2_problem.npz")))
 g = dict(np.load(os.path.join(gold, "th2_uniform.npz")))
 eng = Engine(0)
+eng.set_method(os.environ.get('LASSIM_METHOD', 'dop853'))
 eng.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"], p["pert"], 0.5)
 X = np.random.default_rng(0).uniform(p["lb"], p["ub"], size=(1024, 87))
 r = eng.eval(X, details=True)
