@@ -126,6 +126,33 @@ int lassim_trajectories(lassim_handle *h, int N, const double *X, double *Y,
                         int *status);
 
 /*
+ * Peripheral genes fitted against a FIXED core (BASELINE.json config 5).  The
+ * reference has no implementation of this (its README lists it as future
+ * work, README.md:77-80), so the definition is by analogy with the core
+ * problem: gene p obeys
+ *     dx_p/dt = -lambda_p x_p + vmax_p / (1 + exp(-sum_j w_pj x_j(t)))
+ * where x_j(t) is the core trajectory produced by `core_x` (a decision vector
+ * of the problem currently set, which must have no more than 31 genes); the
+ * joint (n+1)-state system is integrated from (y0_core, y0_p) over the core's
+ * sample times and the cost is the time-series cost (core_problem.py:89-90) of
+ * the peripheral state alone:  sum_t (data_p[t] - x_p(t)/max_t x_p)^2 / sigma_p^2.
+ *   genes    number of peripheral genes
+ *   data[genes*T], sigma[genes], y0[genes]
+ *   mask[genes*n] non-zero where core gene j may regulate gene p (NULL = all)
+ * A candidate is xp = [lambda_p, vmax_p, w_p(n)] (entries outside the mask are
+ * ignored); gene[i] says which gene candidate i belongs to, so one call can
+ * evaluate the populations of many genes.  Host buffers.
+ */
+int lassim_set_peripheral(lassim_handle *h, const double *core_x, int genes,
+                          const double *data, const double *sigma, const double *y0,
+                          const unsigned char *mask);
+int lassim_eval_peripheral(lassim_handle *h, int N, const int *gene, const double *Xp,
+                           double *cost, int *status);
+/* Joint trajectories Y[N*T*(n+1)] of the same candidates (last column = x_p). */
+int lassim_peripheral_trajectories(lassim_handle *h, int N, const int *gene,
+                                   const double *Xp, double *Y);
+
+/*
  * End states of the knock-down part of the LAST lassim_eval / _eval_device
  * call: E[N*K*n], K = lassim_trajectories_per_candidate(); slot 0 is unused
  * (time series), 1..U the controls in order of first appearance, 1+U+i the

@@ -66,6 +66,15 @@ def load_library():
     lib.lassim_eval_device_noalloc.restype = ctypes.c_int
     lib.lassim_trajectories.argtypes = [H, ctypes.c_int, c_double_p, c_double_p,
                                         c_int_p]
+    lib.lassim_set_peripheral.argtypes = [H, c_double_p, ctypes.c_int, c_double_p, c_double_p,
+                                          c_double_p, c_ubyte_p]
+    lib.lassim_eval_peripheral.argtypes = [H, ctypes.c_int, c_int_p, c_double_p, c_double_p,
+                                           c_int_p]
+    lib.lassim_peripheral_trajectories.argtypes = [H, ctypes.c_int, c_int_p, c_double_p,
+                                                   c_double_p]
+    for name in ("lassim_set_peripheral", "lassim_eval_peripheral",
+                 "lassim_peripheral_trajectories"):
+        getattr(lib, name).restype = ctypes.c_int
     lib.lassim_last_end_states.argtypes = [H, ctypes.c_int, c_double_p]
     lib.lassim_last_traj_steps.argtypes = [H, ctypes.c_int, c_uint_p]
     lib.lassim_flops_per_attempt.argtypes = [H]
@@ -236,6 +245,66 @@ class Engine:
                                                   st.ctypes.data_as(c_int_p)),
                     "lassim_trajectories")
         return (Y, st) if return_status else Y
+
+    # -- peripheral genes against a fixed core ------------------------------
+    def set_peripheral(self, core_x, data, sigma, y0, mask=None):
+        """Peripheral genes of the problem currently set: core_x[dim], data[genes, T],
+        sigma[genes], y0[genes], mask[genes, n] (None = every core gene may regulate)."""
+        core_x = _f64(core_x).reshape(-1)
+        if core_x.size != self.dim:
+            raise ValueError("core vector has %d entries, the core problem has %d"
+                             % (core_x.size, self.dim))
+        data = _f64(data)
+        if data.ndim != 2 or data.shape[1] != self.T:
+            raise ValueError("peripheral data shape %s is not (genes, T=%d)" % (data.shape, self.T))
+        genes = data.shape[0]
+        sigma = _f64(np.broadcast_to(_f64(sigma), (genes,)))
+        y0 = _f64(y0).reshape(-1)
+        if y0.size != genes:
+            raise ValueError("y0 has %d entries for %d genes" % (y0.size, genes))
+        mp = None
+        if mask is not None:
+            mask = np.ascontiguousarray(np.asarray(mask) != 0, dtype=np.uint8)
+            if mask.shape != (genes, self.n):
+                raise ValueError("mask shape %s is not (genes, n)=(%d, %d)"
+                                 % (mask.shape, genes, self.n))
+            mp = mask.ctypes.data_as(c_ubyte_p)
+        self._check(self._lib.lassim_set_peripheral(self._h, _dp(core_x), genes, _dp(data),
+                                                    _dp(sigma), _dp(y0), mp),
+                    "lassim_set_peripheral")
+        self.p_genes = genes
+
+    def _peripheral_args(self, gene, Xp):
+        Xp = _f64(Xp)
+        if Xp.ndim == 1:
+            Xp = Xp.reshape(1, -1)
+        if Xp.shape[1] != self.n + 2:
+            raise ValueError("peripheral candidates have %d entries, expected n + 2 = %d"
+                             % (Xp.shape[1], self.n + 2))
+        gene = np.ascontiguousarray(np.broadcast_to(np.asarray(gene, dtype=np.int32),
+                                                    (Xp.shape[0],)))
+        return gene, Xp
+
+    def eval_peripheral(self, gene, Xp, return_status=False):
+        """cost[N] of peripheral candidates Xp[N, n + 2] = [lambda, vmax, w(n)];
+        gene[N] (or one int) says which gene each row belongs to."""
+        gene, Xp = self._peripheral_args(gene, Xp)
+        N = Xp.shape[0]
+        cost = np.empty(N)
+        st = np.empty(N, dtype=np.int32)
+        self._check(self._lib.lassim_eval_peripheral(
+            self._h, N, gene.ctypes.data_as(c_int_p), _dp(Xp), _dp(cost),
+            st.ctypes.data_as(c_int_p)), "lassim_eval_peripheral")
+        return (cost, st) if return_status else cost
+
+    def peripheral_trajectories(self, gene, Xp):
+        gene, Xp = self._peripheral_args(gene, Xp)
+        N = Xp.shape[0]
+        Y = np.empty((N, self.T, self.n + 1))
+        self._check(self._lib.lassim_peripheral_trajectories(
+            self._h, N, gene.ctypes.data_as(c_int_p), _dp(Xp), _dp(Y)),
+            "lassim_peripheral_trajectories")
+        return Y
 
     def last_end_states(self, N):
         K = self.trajectories_per_candidate

@@ -47,6 +47,13 @@ struct DevProblem {
     const int *knock_ctrl;    // [n] trajectory index of row i's control
     double pert_factor, rtol, atol;
     unsigned int max_steps;
+    // peripheral-gene problems (PERIPH kernels): the core occupies states
+    // 0..n-2 with fixed parameters, state n-1 is one peripheral gene
+    const double *core_x;     // [2*(n-1) + nnz_core] decision vector of the core
+    const unsigned char *pmask;   // [genes*(n-1)] allowed regulators of each gene
+    const double *pdata;      // [genes*T] normalised series of each gene
+    const double *psigma2;    // [genes]
+    const double *py0;        // [genes]
 };
 
 struct DevBatch {
@@ -64,12 +71,20 @@ struct DevBatch {
     int *done;                // [N]   zeroed before launch
     unsigned int *work_counter;    // zeroed before launch
     const unsigned int *order;     // optional permutation of work items
+    const int *pgene;         // [N] peripheral gene of each candidate (PERIPH kernels)
 };
 
 enum { kMethodDP45 = 0, kMethodDOP853 = 1 };
 
 // threads per CTA for a group of L lanes
 constexpr int threads_for(int L) { return L > 32 ? L : (L == 4 ? 256 : 128); }
+
+// minimum resident CTAs per SM asked of the compiler for the warp-slice shapes
+// (register budget = 65536 / (threads * blocks))
+#ifndef LASSIM_MIN_BLOCKS
+#define LASSIM_MIN_BLOCKS 4
+#endif
+constexpr int min_blocks_for(int L) { return (L == 16 || L == 32) ? LASSIM_MIN_BLOCKS : 1; }
 
 // doubles of shared memory in front of the groups' exchange lines:
 // 64 (2^(j/64) table) + 32 (reduction / broadcast scratch of a CTA-wide group)
@@ -149,6 +164,30 @@ struct DenseW {
                 if (ok[r] && j < n) {
                     const int id = P.kidx[g * n + j];
                     if (id >= 0) wv = x[2 * n + id];
+                }
+                w[r][j] = wv * scale;
+            }
+        }
+    }
+    // Peripheral problems: core rows from the fixed core vector, the last state's
+    // row from the candidate xp = [lambda_p, vmax_p, w_p(n-1)], masked per gene.
+    __device__ __forceinline__ void load_peripheral(const DevProblem &P, const double *xp,
+                                                    int gene, int lg, const bool (&ok)[R],
+                                                    double scale) {
+        const int nc = P.n - 1;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int g = lg * R + r;
+#pragma unroll
+            for (int j = 0; j < NC; ++j) {
+                double wv = 0.0;
+                if (ok[r] && j < nc) {
+                    if (g < nc) {
+                        const int id = P.kidx[g * nc + j];
+                        if (id >= 0) wv = P.core_x[2 * nc + id];
+                    } else if (P.pmask[(size_t)gene * nc + j]) {
+                        wv = xp[2 + j];
+                    }
                 }
                 w[r][j] = wv * scale;
             }
@@ -341,8 +380,8 @@ struct Grp {
 };
 
 // ---------------------------------------------------------------- kernel
-template <int L, int R, class WT, int METHOD, bool FAST>
-__global__ void __launch_bounds__(threads_for(L))
+template <int L, int R, class WT, int METHOD, bool FAST, bool PERIPH = false>
+__global__ void __launch_bounds__(threads_for(L), min_blocks_for(L))
 grn_cost_kernel(const DevProblem P, const DevBatch B) {
     constexpr int NP = L * R;
     constexpr int STRIDE = NP + 2;   // 16 B skew between groups: no bank conflicts
@@ -381,7 +420,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
     }
 
     bool active = false, exhausted = false;
-    int c = 0, k = 0, ti = 1, nt = 2, cur = 0, st = 0;
+    int c = 0, k = 0, ti = 1, nt = 2, cur = 0, st = 0, pg = 0;
     unsigned nacc = 0, nrej = 0;
     bool rejected = false;
     double t = 0.0, h = 0.0, tend = 0.0;
@@ -414,20 +453,43 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                 k = (int)(w / (unsigned)B.N);
                 c = (int)(w - (unsigned)k * (unsigned)B.N);
                 const double *x = B.X + (size_t)c * P.dim;
-                const int prefix = P.traj_prefix[k];
+                if constexpr (PERIPH) {
+                    // joint system: fixed core (states 0..n-2) + one peripheral gene
+                    const int nc = n - 1;
+                    pg = B.pgene[c];
 #pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    const int g = lg * R + r;
-                    lam[r] = 0.0; vm[r] = 0.0; y[r] = 0.0;
-                    if (gene_ok[r]) {
-                        double l = x[g];
-                        if (g < prefix) l *= P.pert[(size_t)g * (n + 2) + g];
-                        lam[r] = l;
-                        vm[r] = x[n + g];
-                        y[r] = P.y0[g];
+                    for (int r = 0; r < R; ++r) {
+                        const int g = lg * R + r;
+                        lam[r] = 0.0; vm[r] = 0.0; y[r] = 0.0;
+                        if (gene_ok[r]) {
+                            if (g < nc) {
+                                lam[r] = P.core_x[g];
+                                vm[r] = P.core_x[nc + g];
+                                y[r] = P.y0[g];
+                            } else {
+                                lam[r] = x[0];
+                                vm[r] = x[1];
+                                y[r] = P.py0[pg];
+                            }
+                        }
                     }
+                    wts.load_peripheral(P, x, pg, lg, gene_ok, FAST ? kSigScale : 1.0);
+                } else {
+                    const int prefix = P.traj_prefix[k];
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        const int g = lg * R + r;
+                        lam[r] = 0.0; vm[r] = 0.0; y[r] = 0.0;
+                        if (gene_ok[r]) {
+                            double l = x[g];
+                            if (g < prefix) l *= P.pert[(size_t)g * (n + 2) + g];
+                            lam[r] = l;
+                            vm[r] = x[n + g];
+                            y[r] = P.y0[g];
+                        }
+                    }
+                    wts.load(P, x, lg, gene_ok, FAST ? kSigScale : 1.0);
                 }
-                wts.load(P, x, lg, gene_ok, FAST ? kSigScale : 1.0);
                 if (k == 0) { tl = P.times; nt = P.T; }
                 else { tl = P.traj_tt + 2 * k; nt = 2; }
                 t = tl[0];
@@ -558,8 +620,10 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                 double part = 0.0;
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    if (gene_ok[r]) {
-                        const int g = lg * R + r;
+                    const int g = lg * R + r;
+                    // peripheral problems fit the last state only, against the
+                    // series of the candidate's own gene
+                    if (gene_ok[r] && (!PERIPH || g == n - 1)) {
                         double m = -CUDART_INF;
                         bool isnan_ = false;
                         for (int s = 0; s < P.T; ++s) {
@@ -568,9 +632,11 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                             m = fmax(m, v);
                         }
                         if (isnan_) m = CUDART_NAN;   // numpy.amax propagates NaN
-                        const double s2 = P.sigma2[g];
+                        const double s2 = PERIPH ? P.psigma2[pg] : P.sigma2[g];
                         for (int s = 0; s < P.T; ++s) {
-                            const double d = P.data[s * n + g] - Yc[s * n + g] / m;
+                            const double ref = PERIPH ? P.pdata[(size_t)pg * P.T + s]
+                                                      : P.data[s * n + g];
+                            const double d = ref - Yc[s * n + g] / m;
                             part += d * d / s2;
                         }
                     }

@@ -57,6 +57,12 @@ struct lassim_handle {
     DevBuf<double> d_times, d_y0, d_data, d_sigma2, d_pert, d_traj_tt;
     DevBuf<int> d_kidx, d_row_ptr, d_col_idx, d_traj_prefix, d_knock_ctrl;
 
+    // peripheral genes fitted against a fixed core (lassim_set_peripheral)
+    int p_genes = 0;
+    DevBuf<double> d_core_x, d_pdata, d_psigma2, d_py0;
+    DevBuf<unsigned char> d_pmask;
+    DevBuf<int> d_pgene;
+
     // scratch
     DevBuf<double> d_X, d_cost, d_cost_main, d_pert_cost, d_Y, d_E, d_probe;
     DevBuf<unsigned char> d_zero;   // work counter | done | status | counters
@@ -202,13 +208,48 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
     return false;
 }
 
+// Peripheral problems integrate n + 1 states (fixed core + one gene) with the
+// dense warp-slice kernels; NC covers the n core columns.
+template <int L, int NC>
+kernel_fn peripheral_kernel(int method) {
+    if (method == kMethodDP45)
+        return grn_cost_kernel<L, 1, DenseW<1, NC>, kMethodDP45, true, true>;
+    return grn_cost_kernel<L, 1, DenseW<1, NC>, kMethodDOP853, true, true>;
+}
+
+bool choose_peripheral_kernel(const lassim_handle *h, KernelChoice *out) {
+    const int nc = h->n, np = nc + 1, method = h->method;
+    const int cols = (nc + 3) & ~3;
+    if (np <= 16) {
+        kernel_fn fn = cols <= 4 ? peripheral_kernel<16, 4>(method)
+                     : cols <= 8 ? peripheral_kernel<16, 8>(method)
+                     : cols <= 12 ? peripheral_kernel<16, 12>(method)
+                                  : peripheral_kernel<16, 16>(method);
+        *out = {fn, 16, 1, "peripheral dense 16x1"};
+        return true;
+    }
+    if (np <= 32) {
+        kernel_fn fn = cols <= 24 ? peripheral_kernel<32, 24>(method)
+                                  : peripheral_kernel<32, 32>(method);
+        *out = {fn, 32, 1, "peripheral dense 32x1"};
+        return true;
+    }
+    return false;
+}
+
 int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
-                cudaStream_t s) {
+                cudaStream_t s, const int *d_pgene = nullptr) {
+    const bool periph = d_pgene != nullptr;
     KernelChoice kc;
-    if (!choose_kernel(h, &kc))
+    if (periph) {
+        if (!choose_peripheral_kernel(h, &kc))
+            return fail(h, LASSIM_E_UNSUPPORTED,
+                        "peripheral genes need a core of at most 31 genes (core has %d)", h->n);
+    } else if (!choose_kernel(h, &kc)) {
         return fail(h, LASSIM_E_UNSUPPORTED,
                     "state size n=%d is outside the kernels built (n <= 1024)", h->n);
-    const int K = h->K, n = h->n;
+    }
+    const int K = periph ? 1 : h->K, n = periph ? h->n + 1 : h->n;
     const ZeroLayout z = zero_layout(N);
     CU(h->d_zero.reserve(z.bytes));
     CU(h->d_cost.reserve(N));
@@ -233,9 +274,12 @@ int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
     P.knock_ctrl = h->d_knock_ctrl.p;
     P.pert_factor = h->pert_factor; P.rtol = h->rtol; P.atol = h->atol;
     P.max_steps = (unsigned int)(h->max_steps > 4000000000LL ? 4000000000LL : h->max_steps);
+    P.core_x = h->d_core_x.p; P.pmask = h->d_pmask.p; P.pdata = h->d_pdata.p;
+    P.psigma2 = h->d_psigma2.p; P.py0 = h->d_py0.p;
+    if (periph) { P.U = 0; P.dim = h->n + 2; P.pert = nullptr; }
 
     DevBatch B;
-    B.N = N; B.mode = mode; B.X = dX;
+    B.N = N; B.mode = mode; B.X = dX; B.pgene = d_pgene;
     B.cost = h->d_cost.p; B.cost_main = h->d_cost_main.p; B.pert_cost = h->d_pert_cost.p;
     B.work_counter = reinterpret_cast<unsigned int *>(h->d_zero.p);
     B.done = reinterpret_cast<int *>(h->d_zero.p + z.off_done);
@@ -324,6 +368,8 @@ int lassim_destroy(lassim_handle *h) {
     h->d_times.release(); h->d_y0.release(); h->d_data.release(); h->d_sigma2.release();
     h->d_pert.release(); h->d_traj_tt.release(); h->d_kidx.release();
     h->d_row_ptr.release(); h->d_col_idx.release();
+    h->d_core_x.release(); h->d_pdata.release(); h->d_psigma2.release(); h->d_py0.release();
+    h->d_pmask.release(); h->d_pgene.release();
     h->d_traj_prefix.release(); h->d_knock_ctrl.release();
     h->d_X.release(); h->d_cost.release(); h->d_cost_main.release();
     h->d_pert_cost.release(); h->d_Y.release(); h->d_E.release(); h->d_probe.release();
@@ -356,6 +402,7 @@ int lassim_set_problem(lassim_handle *h, int n, int T, const double *times,
                             "perturbation row %d has t_end < t_start", i);
     CU(cudaSetDevice(h->device));
     h->has_problem = false;
+    h->p_genes = 0;
     h->n = n; h->T = T; h->pert_factor = pert_factor;
     std::vector<double> sigma2(n);
     for (int i = 0; i < n; ++i) sigma2[i] = sigma[i] * sigma[i];
@@ -535,6 +582,75 @@ int lassim_trajectories(lassim_handle *h, int N, const double *X, double *Y, int
     return LASSIM_OK;
 }
 
+int lassim_set_peripheral(lassim_handle *h, const double *core_x, int genes,
+                          const double *data, const double *sigma, const double *y0,
+                          const unsigned char *mask) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->has_problem) return fail(h, LASSIM_E_STATE, "set_peripheral before set_problem");
+    if (!core_x || genes < 1 || !data || !sigma || !y0)
+        return fail(h, LASSIM_E_INVALID, "set_peripheral: genes=%d or a NULL array", genes);
+    if (h->n > 31)
+        return fail(h, LASSIM_E_UNSUPPORTED,
+                    "peripheral genes need a core of at most 31 genes (core has %d)", h->n);
+    CU(cudaSetDevice(h->device));
+    const int n = h->n, T = h->T;
+    std::vector<double> sigma2(genes);
+    for (int g = 0; g < genes; ++g) sigma2[g] = sigma[g] * sigma[g];
+    std::vector<unsigned char> all;
+    if (!mask) { all.assign((size_t)genes * n, 1); mask = all.data(); }
+    int rc;
+    if ((rc = upload(h, h->d_core_x, core_x, (size_t)h->dim))) return rc;
+    if ((rc = upload(h, h->d_pdata, data, (size_t)genes * T))) return rc;
+    if ((rc = upload(h, h->d_psigma2, sigma2.data(), (size_t)genes))) return rc;
+    if ((rc = upload(h, h->d_py0, y0, (size_t)genes))) return rc;
+    if ((rc = upload(h, h->d_pmask, mask, (size_t)genes * n))) return rc;
+    CU(cudaStreamSynchronize(h->stream));
+    h->p_genes = genes;
+    return LASSIM_OK;
+}
+
+int lassim_eval_peripheral(lassim_handle *h, int N, const int *gene, const double *Xp,
+                           double *cost, int *status) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->has_problem || h->p_genes < 1)
+        return fail(h, LASSIM_E_STATE, "eval_peripheral before set_problem + set_peripheral");
+    if (N < 0 || (N > 0 && (!gene || !Xp || !cost)))
+        return fail(h, LASSIM_E_INVALID, "eval_peripheral: N=%d or a NULL array", N);
+    if (N == 0) return LASSIM_OK;
+    for (int i = 0; i < N; ++i)
+        if (gene[i] < 0 || gene[i] >= h->p_genes)
+            return fail(h, LASSIM_E_INVALID, "eval_peripheral: gene[%d]=%d outside [0,%d)",
+                        i, gene[i], h->p_genes);
+    CU(cudaSetDevice(h->device));
+    cudaStream_t s = h->stream;
+    const int pdim = h->n + 2;
+    CU(h->d_X.reserve((size_t)N * pdim));
+    CU(h->d_pgene.reserve((size_t)N));
+    CU(cudaMemcpyAsync(h->d_X.p, Xp, sizeof(double) * (size_t)N * pdim, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(h->d_pgene.p, gene, sizeof(int) * (size_t)N, cudaMemcpyHostToDevice, s));
+    int rc = launch_eval(h, N, 0, h->d_X.p, nullptr, s, h->d_pgene.p);
+    if (rc) return rc;
+    const ZeroLayout z = zero_layout(N);
+    CU(cudaMemcpyAsync(cost, h->d_cost.p, sizeof(double) * (size_t)N, cudaMemcpyDeviceToHost, s));
+    if (status) CU(cudaMemcpyAsync(status, h->d_zero.p + z.off_status, sizeof(int) * (size_t)N,
+                                   cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    return LASSIM_OK;
+}
+
+int lassim_peripheral_trajectories(lassim_handle *h, int N, const int *gene, const double *Xp,
+                                   double *Y) {
+    double *cost = nullptr;
+    std::vector<double> tmp((size_t)(N > 0 ? N : 0));
+    cost = tmp.data();
+    int rc = lassim_eval_peripheral(h, N, gene, Xp, cost, nullptr);
+    if (rc || N == 0) return rc;
+    if (!Y) return fail(h, LASSIM_E_INVALID, "peripheral_trajectories: Y is NULL");
+    CU(cudaMemcpy(Y, h->d_Y.p, sizeof(double) * (size_t)N * h->T * (h->n + 1),
+                  cudaMemcpyDeviceToHost));
+    return LASSIM_OK;
+}
+
 int lassim_last_end_states(lassim_handle *h, int N, double *E) {
     if (!h) return LASSIM_E_INVALID;
     if (!h->last_had_E || N != h->last_N || !E)
@@ -695,8 +811,10 @@ extern "C" int lassim_eval_device_noalloc(lassim_handle *h, int N, const double 
     P.pert_factor = h->pert_factor; P.rtol = h->rtol; P.atol = h->atol;
     P.max_steps = (unsigned int)(h->max_steps > 4000000000LL ? 4000000000LL : h->max_steps);
 
+    P.core_x = nullptr; P.pmask = nullptr; P.pdata = nullptr; P.psigma2 = nullptr; P.py0 = nullptr;
+
     DevBatch B;
-    B.N = N; B.mode = 0; B.X = dX;
+    B.N = N; B.mode = 0; B.X = dX; B.pgene = nullptr;
     B.cost = dcost;                                           // straight into the caller's buffer
     B.work_counter = reinterpret_cast<unsigned int *>(base);
     B.done = reinterpret_cast<int *>(base + L.off_done);

@@ -191,3 +191,44 @@ def reference_total_cost(x, data, sigma, times, y0, pert_data, pert_factor,
         sol2 = np.array(x, dtype=np.float64)
         p = float(pert(pert_data, n, y0, sol2, vm, mask, ode))
     return pert_factor * p + c, c, p
+
+
+# --------------------------------------------------------------------------
+# Peripheral genes against a fixed core (BASELINE.json config 5).
+# PARITY UNPINNED: the reference has no implementation of this (README.md:77-80
+# lists it as future work), so there is nothing of the reference's to run or to
+# take golden vectors from.  This is the definition by analogy that the CUDA
+# path is checked against: the joint (n+1)-state system through the same LSODA
+# call as a2, and the a3 cost formula applied to the peripheral state alone.
+# --------------------------------------------------------------------------
+def peripheral_cost(xp, core_x, times, y0_core, vector_map, mask, data_p, sigma_p,
+                    y0_p, pmask=None, rtol=None, atol=None, return_traj=False):
+    """xp = [lambda_p, vmax_p, w_p(n)]; core_x = decision vector of the core;
+    data_p[T], sigma_p, y0_p of one peripheral gene; pmask[n] allowed regulators."""
+    n = y0_core.size
+    core_x = np.asarray(core_x, dtype=np.float64)
+    xp = np.asarray(xp, dtype=np.float64)
+    W = np.zeros((n + 1, n + 1))
+    Wc = np.zeros(n * n)
+    Wc[np.asarray(mask, dtype=bool)] = core_x[2 * n:]
+    W[:n, :n] = Wc.reshape(n, n)
+    w_p = xp[2:].copy()
+    if pmask is not None:
+        w_p = np.where(np.asarray(pmask, dtype=bool), w_p, 0.0)
+    W[n, :n] = w_p
+    lam = np.concatenate([core_x[:n], xp[:1]])
+    vmax = np.concatenate([core_x[n:2 * n], xp[1:2]])
+    y0 = np.concatenate([y0_core, [y0_p]])
+    kw = {}
+    if rtol is not None:
+        kw["rtol"] = rtol
+    if atol is not None:
+        kw["atol"] = atol
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        Y = integrate.odeint(lassim_function, y0, times, args=(lam, vmax, W),
+                             mxstep=int(1e8), **kw)
+    xpt = Y[:, n]
+    with np.errstate(all="ignore"):
+        cost = float(np.sum((data_p - xpt / np.amax(xpt)) ** 2 / sigma_p ** 2))
+    return (cost, Y) if return_traj else cost

@@ -1,0 +1,97 @@
+"""Peripheral genes against a fixed core (BASELINE.json config 5).  The reference
+has no implementation (parity unpinned); the check is against the definition
+by analogy in oracle/lassim_oracle.py::peripheral_cost (joint system through
+LSODA, time-series cost of the peripheral state)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import REPO
+
+sys.path.insert(0, os.path.join(REPO, "oracle"))
+import lassim_oracle as orc  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+def mild_core(th2, seed=3):
+    rng = np.random.default_rng(seed)
+    n, nnz = 12, int(th2["mask"].sum())
+    return np.concatenate([rng.uniform(0.05, 0.6, n), rng.uniform(0.2, 1.5, n),
+                           rng.uniform(-1.5, 1.5, nnz)])
+
+
+def peripheral_data(th2, genes, seed=5):
+    rng = np.random.default_rng(seed)
+    T = th2["times"].size
+    data = rng.uniform(0.1, 1.0, (genes, T))
+    sigma = rng.uniform(0.1, 0.4, genes)
+    y0 = rng.uniform(0.1, 1.2, genes)
+    mask = rng.random((genes, 12)) < 0.6
+    mask[:, 0] = True
+    Xp = np.concatenate([rng.uniform(0.05, 1.0, (genes, 1)), rng.uniform(0.2, 1.5, (genes, 1)),
+                         rng.uniform(-2, 2, (genes, 12))], axis=1)
+    return data, sigma, y0, mask, Xp
+
+
+@pytest.mark.parametrize("method", ["dop853", "dp45"])
+def test_peripheral_cost_matches_definition(th2, method):
+    from lassim_b200 import Engine
+    eng = Engine(0)
+    eng.set_method(method)
+    eng.set_problem(th2["data"], th2["sigma"], th2["times"], th2["y0"], th2["mask"], None, 0.0)
+    core_x = mild_core(th2)
+    genes = 7
+    data, sigma, y0, mask, Xp = peripheral_data(th2, genes)
+    eng.set_peripheral(core_x, data, sigma, y0, mask)
+    gene = np.arange(genes, dtype=np.int32)
+    cost, status = eng.eval_peripheral(gene, Xp, return_status=True)
+    assert (status == 0).all()
+    Y = eng.peripheral_trajectories(gene, Xp)
+    core_Y = eng.trajectories(core_x)[0]
+    for g in range(genes):
+        want, Yt = orc.peripheral_cost(Xp[g], core_x, th2["times"], th2["y0"], th2["vector_map"],
+                                       th2["mask"], data[g], sigma[g], y0[g], mask[g],
+                                       rtol=1e-13, atol=1e-13, return_traj=True)
+        assert cost[g] == pytest.approx(want, rel=1e-6)
+        np.testing.assert_allclose(Y[g], Yt, rtol=1e-5, atol=1e-7)
+        # the core part of the joint system is the core trajectory
+        np.testing.assert_allclose(Y[g][:, :12], core_Y, rtol=1e-6, atol=1e-9)
+    # same gene twice, different candidates, in one call; masked weights are ignored
+    X2 = Xp[[2, 2]].copy()
+    X2[1, 2:][~mask[2]] += 5.0
+    c2 = eng.eval_peripheral(2, X2)
+    assert c2[0] == cost[2] and c2[1] == cost[2]
+    with pytest.raises(Exception):
+        eng.eval_peripheral(genes, Xp[:1])
+    eng.close()
+
+
+def test_peripheral_sweep_de(th2):
+    """A small sweep: every generation of every gene in one launch; the fit of
+    synthetic peripheral genes (generated from hidden parameters) improves."""
+    from lassim_b200.core.core_problem import CoreProblemFactory
+    from lassim_b200.core.functions.common_functions import odeint1e8_lassim
+    from lassim_b200.core.peripheral_problem import PeripheralSweep
+    p = th2
+    prob = CoreProblemFactory.new_instance((p["data"], p["sigma"], p["times"]), p["y0"],
+                                           odeint1e8_lassim).build(
+        87, (list(p["lb"]), list(p["ub"])), (p["vector_map"], p["mask"]))
+    core_x = mild_core(p)
+    genes = 24
+    data, sigma, y0, mask, hidden = peripheral_data(p, genes, seed=11)
+    # make the data reachable: series of the hidden candidates themselves
+    for g in range(genes):
+        _, Y = orc.peripheral_cost(hidden[g], core_x, p["times"], p["y0"], p["vector_map"],
+                                   p["mask"], data[g], sigma[g], y0[g], mask[g], return_traj=True)
+        data[g] = Y[:, 12] / Y[:, 12].max()
+    sweep = PeripheralSweep(prob, core_x, data, 0.2, y0, mask)
+    x0, f0 = sweep.solve_de(individuals=12, generations=0, seed=1)
+    x1, f1 = sweep.solve_de(individuals=12, generations=15, seed=1)
+    assert sweep.evaluations == genes * 12 * (1 + 16)
+    assert (f1 <= f0).all() and np.median(f1) < 0.25 * np.median(f0)
+    one = sweep.problem(5)
+    assert one._objfun_impl(tuple(x1[5]))[0] == pytest.approx(f1[5], rel=1e-12)
+    assert sweep.evaluate(np.full(genes, 0), hidden)[0] == pytest.approx(0.0, abs=1e-9)

@@ -1,0 +1,73 @@
+"""Timing of BASELINE.json's other configs (3, 4, 5) on one B200, with the CPU
+reference on a bounded sample where one exists.  Writes gpurun_out/configs.json.
+(bench.py measures config 2, the headline; these are supporting numbers.)"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, REPO)
+from lassim_b200 import Engine  # noqa: E402
+from lassim_b200.synthetic import stiff_population, synthetic_problem, uniform_population  # noqa: E402
+
+out = {}
+eng = Engine(0)
+peak = eng.fp64_peak_tflops(200000)
+
+
+def run(name, p, X, pert, reps=2):
+    eng.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"],
+                    p["pert"] if pert else None, 0.5)
+    eng.eval(X[:min(len(X), 64)])
+    best = None
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        r = eng.eval(X, details=True)
+        wall = time.perf_counter() - t0
+        ms = eng.last_kernel_ms()
+        if best is None or ms < best[0]:
+            best = (ms, wall, r)
+    ms, wall, r = best
+    att = int(r["counters"][:, :2].sum())
+    steps = eng.last_traj_steps(len(X))
+    out[name] = {"candidates": len(X), "trajectories_per_candidate": eng.trajectories_per_candidate,
+                 "kernel": eng.kernel_name, "kernel_ms": ms, "wall_s": wall,
+                 "evals_per_s": len(X) / wall, "step_attempts": att,
+                 "rejected_fraction": float(r["counters"][:, 1].sum() / max(att, 1)),
+                 "longest_trajectory_attempts": int(steps.max()),
+                 "achieved_tflops": att * eng.flops_per_attempt / (ms * 1e-3) / 1e12,
+                 "fp64_peak_tflops": peak, "status_not_ok": int((r["status"] != 0).sum())}
+    print(name, json.dumps(out[name]), flush=True)
+
+
+p50 = synthetic_problem(50, seed=50)
+run("config3_syn50_8x128", p50, uniform_population(p50["lb"], p50["ub"], 1024, seed=50), True)
+p200 = synthetic_problem(200, seed=200)
+pop = int(os.environ.get("LASSIM_C4_POP", "512"))
+run("config4_syn200_stiff_pop%d" % pop, p200, stiff_population(p200, pop, seed=200), True, reps=1)
+
+# config 5: 10,000 peripheral genes against a fixed Th2 core
+th2 = dict(np.load(os.path.join(REPO, "tests", "golden", "th2_problem.npz")))
+g = dict(np.load(os.path.join(REPO, "tests", "golden", "th2_late.npz")))
+eng.set_problem(th2["data"], th2["sigma"], th2["times"], th2["y0"], th2["mask"], None, 0.0)
+core_x = g["X"][int(np.argmin(g["ref_cost_main"]))]
+G, NP = 10000, 16
+rng = np.random.default_rng(5)
+data = rng.uniform(0.05, 1.0, (G, 6)); data /= data.max(axis=1, keepdims=True)
+eng.set_peripheral(core_x, data, np.full(G, 0.2), rng.uniform(0.05, 1.5, G), None)
+lb = np.concatenate([[0, 0], np.full(12, -20.0)]); ub = np.full(14, 20.0)
+Xp = rng.uniform(lb, ub, size=(G * NP, 14))
+gene = np.repeat(np.arange(G, dtype=np.int32), NP)
+eng.eval_peripheral(gene[:1024], Xp[:1024])
+t0 = time.perf_counter()
+cost, st = eng.eval_peripheral(gene, Xp, return_status=True)
+wall = time.perf_counter() - t0
+out["config5_peripheral_10000x16"] = {"candidates": G * NP, "kernel_ms": eng.last_kernel_ms(),
+                                      "wall_s": wall, "evals_per_s": G * NP / wall,
+                                      "status_not_ok": int((st != 0).sum())}
+print("config5", json.dumps(out["config5_peripheral_10000x16"]), flush=True)
+os.makedirs(os.path.join(REPO, "gpurun_out"), exist_ok=True)
+json.dump(out, open(os.path.join(REPO, "gpurun_out", "configs.json"), "w"), indent=1)
