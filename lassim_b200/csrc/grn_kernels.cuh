@@ -87,11 +87,12 @@ constexpr int threads_for(int L) { return L > 32 ? L : (L == 4 ? 256 : 128); }
 constexpr int min_blocks_for(int L) { return (L == 16 || L == 32) ? LASSIM_MIN_BLOCKS : 1; }
 
 // doubles of shared memory in front of the groups' exchange lines:
-// 64 (2^(j/64) table) + 32 (reduction / broadcast scratch of a CTA-wide group)
-constexpr int kSmemHeader = 96;
+// 256 (2^(j/256) table) + 32 (reduction / broadcast scratch of a CTA-wide group)
+constexpr int kExpTable = 256;
+constexpr int kSmemHeader = kExpTable + 32;
 
-// 2^(j/64), j = 0..63, filled by the host when the engine is created.
-__constant__ double c_exp2_table[64];
+// 2^(j/256), j = 0..255, filled by the host when the engine is created.
+__constant__ double c_exp2_table[kExpTable];
 
 // With the fast logistic the weights are pre-scaled by -log2(e), so the
 // mat-vec delivers t = -z*log2(e) directly.
@@ -104,32 +105,34 @@ __device__ __forceinline__ double logistic_libm(double z) {
     return 1.0 / (1.0 + exp(-z));
 }
 
-// 1 / (1 + 2^t), t = -z*log2(e).  2^t = 2^n * T[j] * 2^f with t = n + j/64 + f,
-// |f| <= 2^-7 (degree-5 Taylor for 2^f - 1, truncation 4e-17); the reciprocal
-// is an SFU seed (MUFU.RCP64H) refined by one third-order FP64 step.  ~3 ulp.
-// |t| is clamped to 1000: below, 2^t vanishes next to 1; above, the result is
-// < 1e-301 where the reference returns vmax*exp(z) or 0 after overflow.
+// 1 / (1 + 2^t), t = -z*log2(e).  With t = n + j/256 + f, |f| <= 2^-9:
+//   2^t = S * (1 + f*p(f)),  S = 2^n * T[j],  p = degree-3 Taylor of (2^f - 1)/f
+// (truncation 4e-17), so the denominator is d = fma(S, f*p, 1 + S): the table
+// value, its exponent scaling and 1 + S depend only on the rounding of t and sit
+// beside the dependent chain  t -> f -> p -> f*p -> d -> 1/d, not on it.  The
+// reciprocal is an SFU seed (MUFU.RCP64H) refined by one third-order FP64 step.
+// ~3 ulp.  |t| >= 1000 (also NaN/inf) selects d = 2^1000 or 1 directly: below
+// -1000, 2^t vanishes next to 1; above, the result is < 1e-301 where the
+// reference returns vmax*exp(z) or 0 after overflow.  The test runs on the high
+// word with integer ops, in parallel with the chain.
 __device__ __forceinline__ double logistic_fast(double t, const double *tab) {
-    // clamp (also catches NaN/inf) with integer ops on the high word: off the
-    // FP64 pipe, shorter than two compare+select pairs on the dependent chain
-    {
-        const int hi = __double2hiint(t);
-        if ((hi & 0x7fffffff) >= 0x408f4000)
-            t = __hiloint2double((hi & 0x80000000) | 0x408f4000, 0);
-    }
-    const double kMagic = 105553116266496.0;   // 1.5 * 2^46: ulp = 1/64
+    const int thi = __double2hiint(t);
+    const bool big = (thi & 0x7fffffff) >= 0x408f4000;
+    const double kMagic = 26388279066624.0;    // 1.5 * 2^44: ulp = 1/256
     const double s = t + kMagic;
     const int ki = __double2loint(s);
     const double f = t - (s - kMagic);
-    const double tj = tab[ki & 63];
+    // beside the chain: S = 2^(ki >> 8) * T[ki & 255] and 1 + S
+    const double tj = tab[ki & (kExpTable - 1)];
+    const double S = __hiloint2double(__double2hiint(tj) + ((ki >> 8) << 20), __double2loint(tj));
+    const double S1 = 1.0 + S;
+    // on the chain
     const double f2 = f * f;
     const double p01 = fma(0.2402265069591007, f, 0.6931471805599453);
     const double p23 = fma(0.009618129107628477, f, 0.05550410866482158);
-    const double p = fma(f2, fma(f2, 0.0013333558146428443, p23), p01);
-    const double v = fma(tj, f * p, tj);
-    const double e = __hiloint2double(__double2hiint(v) + ((ki >> 6) << 20),
-                                      __double2loint(v));
-    const double d = 1.0 + e;
+    const double p = fma(f2, p23, p01);
+    double d = fma(S, f * p, S1);
+    if (big) d = (thi < 0) ? 1.0 : 1.0715086071862673e301;   // 2^1000
     double r;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
     // one third-order step: r*(1 + e0 + e0^2), e0 = 1 - d*r (seed error 2^-23
@@ -397,9 +400,9 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
         (LW == 32) ? 0xffffffffu : (((1u << (LW & 31)) - 1u) << (gw * (LW & 31)));
     const int gid = kWarp ? ((int)(threadIdx.x >> 5) * (32 / LW) + gw) : 0;
     double *tab = smem;
-    double *red = smem + 64;
+    double *red = smem + kExpTable;
     double *ybuf = smem + kSmemHeader + gid * (2 * STRIDE);
-    if (threadIdx.x < 64) tab[threadIdx.x] = c_exp2_table[threadIdx.x];
+    for (int i = threadIdx.x; i < kExpTable; i += blockDim.x) tab[i] = c_exp2_table[i];
     for (int i = lg; i < 2 * STRIDE; i += L) ybuf[i] = 0.0;
     __syncthreads();
 

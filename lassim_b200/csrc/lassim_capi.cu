@@ -147,7 +147,7 @@ struct KernelChoice {
     const char *name;
 };
 
-// dynamic shared memory of one CTA: header (2^(j/64) table, reduction scratch)
+// dynamic shared memory of one CTA: header (2^(j/256) table, reduction scratch)
 // + the groups' double-buffered exchange lines
 size_t smem_bytes(const KernelChoice &kc) {
     const int groups_per_cta = threads_for(kc.L) / kc.L;
@@ -351,8 +351,8 @@ int lassim_create(int device, lassim_handle **out) {
         delete h;
         return fail(nullptr, LASSIM_E_CUDA, "stream/event creation failed");
     }
-    double tab[64];
-    for (int j = 0; j < 64; ++j) tab[j] = exp2((double)j / 64.0);
+    double tab[kExpTable];
+    for (int j = 0; j < kExpTable; ++j) tab[j] = exp2((double)j / (double)kExpTable);
     if (cudaMemcpyToSymbol(c_exp2_table, tab, sizeof(tab)) != cudaSuccess) {
         lassim_destroy(h);
         return fail(nullptr, LASSIM_E_CUDA, "upload of the exp2 table failed");
