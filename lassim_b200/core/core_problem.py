@@ -7,11 +7,12 @@ bounds and the reaction map there and instantiates; copies of a problem re-read
 the statics (core_problem.py:19-28, 94-102, 239-241), so one configuration is
 live per process.
 
-New seam: `objfun_batch(X[N, dim]) -> cost[N]`.  With this package's own ode /
-perturbation plugins it is one kernel launch over all N * (1 + U + n)
-trajectories; `_objfun_impl(x)` is the same path for a batch of one.  With
-user-supplied plugins (any other callable) the toolbox's host formulas are
-applied around them, candidate by candidate.
+New seam: `objfun_batch(X[N, dim]) -> cost[N]`: one kernel launch over all
+N * (1 + U + n) trajectories; `_objfun_impl(x)` is the same path for a batch of
+one.  Evaluation happens on the GPU only: the ode / perturbation functions handed
+to the factory must be this package's own plugins.  A problem can still be BUILT
+around any callable (the toolbox's unit tests do that to exercise the pruning
+logic), but evaluating it raises TypeError - nothing is emulated on the host.
 """
 import numpy as np
 
@@ -72,13 +73,20 @@ class CoreProblem(LassimProblem):
     def _native(self):
         return _is_native(CoreProblem._s_ode_function)
 
+    def _require_native(self):
+        if not self._native():
+            raise TypeError(
+                "this problem was built with ode/perturbation functions that are not "
+                "lassim_b200's GPU plugins ({!r}); costs are evaluated on the GPU only and "
+                "foreign integrators cannot be called from there".format(
+                    CoreProblem._s_ode_function))
+
     def objfun_batch(self, X, details=False):
         """Costs of the rows of X.  Candidates whose integration hit the step
         budget or produced non-finite states get +inf (the toolbox would
         return whatever LSODA left in the buffers)."""
+        self._require_native()
         X = np.atleast_2d(np.asarray(X, dtype=Float))
-        if not self._native():
-            return np.array([self._host_objfun(row) for row in X], dtype=Float)
         eng = self._bound_engine()
         out = eng.eval(X, details=True)
         cost = out["cost"]
@@ -89,27 +97,13 @@ class CoreProblem(LassimProblem):
 
     def trajectories_batch(self, X):
         """Time-series states Y[N, T, n] of the rows of X."""
+        self._require_native()
         X = np.atleast_2d(np.asarray(X, dtype=Float))
         return self._bound_engine().trajectories(X)
 
-    # -- toolbox formulas around a user-supplied ode plugin ----------------
-    def _host_main_cost(self, x):
-        sol = np.fromiter(x, dtype=Float)
-        results = CoreProblem._s_ode_function(
-            self._y0, self._time, sol, self.vector_map, self.vector_map_mask,
-            self._size, self._result)
-        with np.errstate(all="ignore"):
-            norm = results / np.amax(results, axis=0)
-            return float(np.sum(np.power(self._data - norm, 2) / self._sigma2))
-
-    def _host_objfun(self, x):
-        return self._host_main_cost(x)
-
     def _objfun_impl(self, x):
         """Cost of one decision vector as a 1-tuple (core_problem.py:75-92)."""
-        if self._native():
-            return (float(self.objfun_batch(np.asarray(x, dtype=Float)[None, :])[0]),)
-        return (self._host_objfun(x),)
+        return (float(self.objfun_batch(np.asarray(x, dtype=Float)[None, :])[0]),)
 
     def __get_deepcopy__(self):
         return CoreProblem(dim=self.dimension)
@@ -139,14 +133,6 @@ class CoreWithPerturbationsProblem(CoreProblem):
     def _native(self):
         return (_is_native(CoreProblem._s_ode_function) and
                 _is_native(CoreWithPerturbationsProblem._s_pert_function))
-
-    def _host_objfun(self, x):
-        cost = self._host_main_cost(x)
-        sol = np.fromiter(x, dtype=Float)
-        pert_cost = CoreWithPerturbationsProblem._s_pert_function(
-            self._pdata, self._size, self._s_y0, sol, self.vector_map,
-            self.vector_map_mask, CoreProblem._s_ode_function)
-        return self._factor * pert_cost + cost
 
     def __get_deepcopy__(self):
         return CoreWithPerturbationsProblem(dim=self.dimension)

@@ -14,10 +14,11 @@ def perturbation_func_sequential(pert_data, size, y0, sol_vector, vector_map,
     2, and the result is the residual of the least-squares fit of one scalar
     times r to the knock-down matrix.
 
-    When `ode` is this package's own ode plugin all n + U solves and the
-    reduction run in one kernel launch.  With any other callable the generic
-    sequence of `ode` calls is made on the host, exactly as the toolbox does,
-    so user-supplied integrators keep working.  `sol_vector` is not mutated."""
+    All n + U solves and the reduction run in one kernel launch, which is why
+    `ode` must be this package's own ode plugin (the toolbox passes it along only
+    to call it; a foreign integrator cannot be called from the device and
+    raises TypeError - there is no host-side re-implementation to fall back to).
+    `sol_vector` is not mutated."""
     size = int(size)
     pert_data = np.ascontiguousarray(pert_data, dtype=np.float64)
     sol = np.array(sol_vector, dtype=np.float64)
@@ -33,28 +34,9 @@ def perturbation_func_sequential(pert_data, size, y0, sol_vector, vector_map,
         _engine.bind(eng, token, np.zeros((2, size)), np.ones(size), times, y0,
                      mask, pert_data, 1.0)
         return float(eng.eval(sol, details=True)["pert_cost"][0])
-    return _generic(pert_data, size, y0, sol, vector_map, vector_map_mask, ode)
-
-
-def _generic(pert_data, size, y0, sol, vector_map, mask, ode):
-    perts = pert_data[:, :size]
-    times = pert_data[:, size:]
-    diag = np.diagonal(perts)
-    sim = np.empty(size * size)
-    controls = {}
-    scratch = np.empty(size)
-    with np.errstate(all="ignore"):
-        for i in range(size):
-            key = str(times[i])
-            if key not in controls:
-                controls[key] = ode(y0, times[i], sol, vector_map, mask, size, scratch)
-            sol[i] = sol[i] * diag[i]
-            traj = ode(y0, times[i], sol, vector_map, mask, size, scratch)
-            sim[i * size:(i + 1) * size] = traj[-1] / controls[key][-1]
-        sim -= 1.0
-        sim[sim > 2] = 2
-        res = np.linalg.lstsq(sim.reshape(-1, 1), perts.flatten(), rcond=None)[1]
-    return float(res[0])
+    raise TypeError(
+        "perturbation_func_sequential evaluates on the GPU and needs lassim_b200's own "
+        "ode plugin (core.functions.common_functions.odeint1e8_lassim); got {!r}".format(ode))
 
 
 perturbation_func_sequential.__lassim_native__ = True

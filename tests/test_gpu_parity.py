@@ -226,25 +226,26 @@ def test_problem_classes_and_plugins(engine, th2, th2_uniform):
         factory.build(dim, bounds, (p["vector_map"], p["mask"][:-1]))
 
 
-def test_user_supplied_ode_plugin_still_works(th2):
-    """The toolbox's own unit test injects a fake ode function
-    (test/custom/test_core_functions.py:24-25); the seam must keep working."""
+def test_foreign_plugins_are_refused_not_emulated(th2):
+    """The toolbox's unit tests build problems around a fake ode function
+    (test/custom/test_core_functions.py:24-25) to exercise the pruning logic.
+    Building still works; evaluating raises instead of falling back to the host."""
     from lassim_b200.core.core_problem import CoreProblemFactory
+    from lassim_b200.core.functions.perturbation_functions import perturbation_func_sequential
     p = th2
-    calls = []
 
     def fake_ode(y0, t, sol, k_map, mask, size, result):
-        calls.append(sol.copy())
         return np.linspace(1.0, 2.0, t.size * size).reshape(t.size, size)
 
     prob = CoreProblemFactory.new_instance((p["data"], p["sigma"], p["times"]), p["y0"],
                                            fake_ode).build(
         87, (list(p["lb"]), list(p["ub"])), (p["vector_map"], p["mask"]))
-    x = np.arange(87, dtype=float)
-    res = np.linspace(1.0, 2.0, 72).reshape(6, 12)
-    want = np.sum((p["data"] - res / res.max(axis=0)) ** 2 / p["sigma"] ** 2)
-    assert prob._objfun_impl(tuple(x))[0] == pytest.approx(want, rel=1e-14)
-    assert len(calls) == 1
+    assert prob.dimension == 87
+    with pytest.raises(TypeError):
+        prob._objfun_impl(tuple(np.arange(87, dtype=float)))
+    with pytest.raises(TypeError):
+        perturbation_func_sequential(p["pert"], 12, p["y0"], np.zeros(87), p["vector_map"],
+                                     p["mask"], fake_ode)
 
 
 def test_pruned_mask_equals_zero_weight(engine, th2, th2_uniform):

@@ -1,0 +1,59 @@
+"""Parity statistics of the CUDA path against the golden vectors produced by the
+reference's own code, for both integrators.  Writes gpurun_out/parity.json
+(copied to profiles/ when a round's numbers are recorded)."""
+import json
+import os
+import sys
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, REPO)
+from lassim_b200 import Engine  # noqa: E402
+from lassim_b200.synthetic import synthetic_problem  # noqa: E402
+
+gold = os.path.join(REPO, "tests", "golden")
+th2 = dict(np.load(os.path.join(gold, "th2_problem.npz")))
+sets = [("th2_uniform", th2, True), ("th2_late", th2, True),
+        ("syn50", synthetic_problem(50, seed=50), True),
+        ("syn200", synthetic_problem(200, seed=200), False)]
+report = {}
+for method in ("dop853", "dp45"):
+    eng = Engine(0)
+    eng.set_method(method)
+    for name, p, pert in sets:
+        g = dict(np.load(os.path.join(gold, name + ".npz")))
+        eng.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"],
+                        p["pert"] if pert else None, float(g["pert_factor"]))
+        r = eng.eval(g["X"], details=True)
+        Y = eng.trajectories(g["X"])
+        ref, tight = g["ref_cost_main"], g["tight_cost_main"]
+        rel_ref = np.abs(r["cost_main"] - ref) / np.abs(ref)
+        rel_tight = np.abs(r["cost_main"] - tight) / np.abs(tight)
+        ref_tight = np.abs(ref - tight) / np.abs(tight)
+        well = ref_tight <= 1e-7
+        scale = np.abs(g["tight_Y"]).max(axis=1, keepdims=True)
+        terr = (np.abs(Y - g["tight_Y"]) / np.maximum(np.abs(g["tight_Y"]), scale)).max(axis=(1, 2))
+        entry = {
+            "candidates": int(len(ref)), "status_not_ok": int((r["status"] != 0).sum()),
+            "reference_converged (ref vs LSODA 1e-13 <= 1e-7)": int(well.sum()),
+            "cost_main rel vs reference, converged set: max": float(rel_ref[well].max()),
+            "cost_main rel vs reference, converged set: median": float(np.median(rel_ref[well])),
+            "cost_main rel vs reference, all: fraction <= 1e-6": float((rel_ref <= 1e-6).mean()),
+            "cost_main rel vs tight, all: max": float(rel_tight.max()),
+            "cost_main rel vs tight, all: median": float(np.median(rel_tight)),
+            "reference rel vs tight, all: max": float(ref_tight.max()),
+            "trajectory mixed-relative error vs tight, converged set: max": float(terr[well].max()),
+            "step attempts (sum over trajectories)": int(r["counters"][:, :2].sum()),
+        }
+        if pert:
+            tp, rp = g["tight_pert_cost"], g["ref_pert_cost"]
+            entry["knock-down cost rel vs tight: median (ill-conditioned, reported not gated)"] = \
+                float(np.nanmedian(np.abs(r["pert_cost"] - tp) / np.abs(tp)))
+            entry["reference knock-down cost rel vs tight: median"] = \
+                float(np.nanmedian(np.abs(rp - tp) / np.abs(tp)))
+        report["%s / %s" % (name, method)] = entry
+        print(name, method, json.dumps(entry), flush=True)
+    eng.close()
+os.makedirs(os.path.join(REPO, "gpurun_out"), exist_ok=True)
+json.dump(report, open(os.path.join(REPO, "gpurun_out", "parity.json"), "w"), indent=1)
