@@ -48,7 +48,7 @@ import lassim_oracle as orc  # noqa: E402
 def _load_synth():
     import importlib.util
     spec = importlib.util.spec_from_file_location(
-        "lassim_synthetic", os.path.join(REPO, "lassim_b200", "synthetic.py"))
+        "lassim_workloads", os.path.join(REPO, "tools", "workloads.py"))
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     return mod

@@ -7,6 +7,8 @@ import pytest
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if REPO not in sys.path:
     sys.path.insert(0, REPO)
+if os.path.join(REPO, "tools") not in sys.path:
+    sys.path.insert(0, os.path.join(REPO, "tools"))      # workloads.py (seeded test problems)
 GOLDEN = os.path.join(REPO, "tests", "golden")
 
 

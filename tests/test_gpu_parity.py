@@ -322,7 +322,7 @@ def test_small_and_ragged_problems_match_oracle(engine, n, T, pert, density):
 def test_synthetic_50_gene_golden(engine):
     """BASELINE config 3's problem (50 genes, in-degree 5): reference outputs in
     tests/golden/syn50.npz."""
-    from lassim_b200.synthetic import synthetic_problem
+    from workloads import synthetic_problem
     p = synthetic_problem(50, seed=50)
     g = load_golden("syn50")
     engine.set_tolerances()
@@ -353,7 +353,7 @@ def test_synthetic_50_gene_golden(engine):
 def test_synthetic_200_gene_golden(engine):
     """BASELINE config 4's problem (200 genes, in-degree 5, stiff regime):
     time-series part against the reference outputs in tests/golden/syn200.npz."""
-    from lassim_b200.synthetic import synthetic_problem
+    from workloads import synthetic_problem
     p = synthetic_problem(200, seed=200)
     g = load_golden("syn200")
     engine.set_tolerances()

@@ -10,8 +10,9 @@ import numpy as np
 
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, REPO)
+sys.path.insert(0, os.path.join(REPO, "tools"))
 from lassim_b200 import Engine  # noqa: E402
-from lassim_b200.synthetic import stiff_population, synthetic_problem, uniform_population  # noqa: E402
+from workloads import stiff_population, synthetic_problem, uniform_population  # noqa: E402
 
 out = {}
 eng = Engine(0)

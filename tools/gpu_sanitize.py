@@ -3,8 +3,9 @@ import os, sys
 import numpy as np
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, REPO)
+sys.path.insert(0, os.path.join(REPO, "tools"))
 from lassim_b200 import Engine
-from lassim_b200.synthetic import synthetic_problem
+from workloads import synthetic_problem
 th2 = dict(np.load(os.path.join(REPO, "tests", "golden", "th2_problem.npz")))
 g = dict(np.load(os.path.join(REPO, "tests", "golden", "th2_late.npz")))
 for method in ("dop853", "dp45"):

@@ -9,8 +9,9 @@ import numpy as np
 
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, REPO)
+sys.path.insert(0, os.path.join(REPO, "tools"))
 from lassim_b200 import Engine  # noqa: E402
-from lassim_b200.synthetic import synthetic_problem  # noqa: E402
+from workloads import synthetic_problem  # noqa: E402
 
 gold = os.path.join(REPO, "tests", "golden")
 th2 = dict(np.load(os.path.join(gold, "th2_problem.npz")))

@@ -1,7 +1,7 @@
 """
 Seeded workloads named by BASELINE.json's configs.  Used by
-bench.py, the tests and the golden-vector generator; never by the evaluation
-path itself.
+the tests, the tools and the golden-vector generator; not part of the product
+package.
 
   synthetic_problem(50, seed=50)   config 3: 50 genes, in-degree 5, nnz 250
   synthetic_problem(200, seed=200) config 4: 200 genes, in-degree 5, nnz 1000
