@@ -73,6 +73,19 @@ struct lassim_handle {
 
 namespace {
 
+// Makes the handle's device current for the duration of a call and puts the
+// caller's device back afterwards (a host application may be driving several).
+struct DeviceGuard {
+    int prev = -1;
+    cudaError_t err;
+    explicit DeviceGuard(int device) {
+        err = cudaGetDevice(&prev);
+        if (err == cudaSuccess && prev != device) err = cudaSetDevice(device);
+        else if (err == cudaSuccess) prev = -1;      // already current: nothing to restore
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
 int fail(lassim_handle *h, int code, const char *fmt, ...) {
     char buf[512];
     va_list ap;
@@ -332,9 +345,9 @@ int lassim_create(int device, lassim_handle **out) {
                     e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
     if (device < 0 || device >= count)
         return fail(nullptr, LASSIM_E_INVALID, "device %d out of range [0,%d)", device, count);
-    e = cudaSetDevice(device);
-    if (e != cudaSuccess)
-        return fail(nullptr, LASSIM_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+    DeviceGuard guard_(device);
+    if (guard_.err != cudaSuccess)
+        return fail(nullptr, LASSIM_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(guard_.err));
     cudaDeviceProp prop;
     e = cudaGetDeviceProperties(&prop, device);
     if (e != cudaSuccess)
@@ -363,7 +376,7 @@ int lassim_create(int device, lassim_handle **out) {
 
 int lassim_destroy(lassim_handle *h) {
     if (!h) return LASSIM_OK;
-    cudaSetDevice(h->device);
+    DeviceGuard guard_(h->device);
     cudaStreamSynchronize(h->stream);
     h->d_times.release(); h->d_y0.release(); h->d_data.release(); h->d_sigma2.release();
     h->d_pert.release(); h->d_traj_tt.release(); h->d_kidx.release();
@@ -400,7 +413,8 @@ int lassim_set_problem(lassim_handle *h, int n, int T, const double *times,
             if (!(pert[(size_t)i * (n + 2) + n + 1] >= pert[(size_t)i * (n + 2) + n]))
                 return fail(h, LASSIM_E_UNSUPPORTED,
                             "perturbation row %d has t_end < t_start", i);
-    CU(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
     h->has_problem = false;
     h->p_genes = 0;
     h->n = n; h->T = T; h->pert_factor = pert_factor;
@@ -461,7 +475,8 @@ int lassim_set_mask(lassim_handle *h, const unsigned char *mask) {
     if (!h) return LASSIM_E_INVALID;
     if (!h->has_problem) return fail(h, LASSIM_E_STATE, "set_mask before set_problem");
     if (!mask) return fail(h, LASSIM_E_INVALID, "mask is NULL");
-    CU(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
     return upload_mask(h, mask);
 }
 
@@ -514,7 +529,8 @@ int lassim_eval_device(lassim_handle *h, int N, const double *dX, double *dcost,
     if (N < 0 || (N > 0 && (!dX || !dcost)))
         return fail(h, LASSIM_E_INVALID, "eval: N=%d, X or cost is NULL", N);
     if (N == 0) return LASSIM_OK;
-    CU(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
     cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
     int rc = launch_eval(h, N, 0, dX, nullptr, s);
     if (rc) return rc;
@@ -539,7 +555,8 @@ int lassim_eval(lassim_handle *h, int N, const double *X, double *cost,
     if (N < 0 || (N > 0 && (!X || !cost)))
         return fail(h, LASSIM_E_INVALID, "eval: N=%d, X or cost is NULL", N);
     if (N == 0) return LASSIM_OK;
-    CU(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
     cudaStream_t s = h->stream;
     CU(h->d_X.reserve((size_t)N * h->dim));
     CU(cudaMemcpyAsync(h->d_X.p, X, sizeof(double) * (size_t)N * h->dim,
@@ -566,7 +583,8 @@ int lassim_trajectories(lassim_handle *h, int N, const double *X, double *Y, int
     if (N < 0 || (N > 0 && (!X || !Y)))
         return fail(h, LASSIM_E_INVALID, "trajectories: N=%d, X or Y is NULL", N);
     if (N == 0) return LASSIM_OK;
-    CU(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
     cudaStream_t s = h->stream;
     CU(h->d_X.reserve((size_t)N * h->dim));
     CU(cudaMemcpyAsync(h->d_X.p, X, sizeof(double) * (size_t)N * h->dim,
@@ -592,7 +610,8 @@ int lassim_set_peripheral(lassim_handle *h, const double *core_x, int genes,
     if (h->n > 31)
         return fail(h, LASSIM_E_UNSUPPORTED,
                     "peripheral genes need a core of at most 31 genes (core has %d)", h->n);
-    CU(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
     const int n = h->n, T = h->T;
     std::vector<double> sigma2(genes);
     for (int g = 0; g < genes; ++g) sigma2[g] = sigma[g] * sigma[g];
@@ -621,7 +640,8 @@ int lassim_eval_peripheral(lassim_handle *h, int N, const int *gene, const doubl
         if (gene[i] < 0 || gene[i] >= h->p_genes)
             return fail(h, LASSIM_E_INVALID, "eval_peripheral: gene[%d]=%d outside [0,%d)",
                         i, gene[i], h->p_genes);
-    CU(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
     cudaStream_t s = h->stream;
     const int pdim = h->n + 2;
     CU(h->d_X.reserve((size_t)N * pdim));
@@ -640,12 +660,13 @@ int lassim_eval_peripheral(lassim_handle *h, int N, const int *gene, const doubl
 
 int lassim_peripheral_trajectories(lassim_handle *h, int N, const int *gene, const double *Xp,
                                    double *Y) {
-    double *cost = nullptr;
-    std::vector<double> tmp((size_t)(N > 0 ? N : 0));
-    cost = tmp.data();
-    int rc = lassim_eval_peripheral(h, N, gene, Xp, cost, nullptr);
+    if (!h) return LASSIM_E_INVALID;
+    if (N > 0 && !Y) return fail(h, LASSIM_E_INVALID, "peripheral_trajectories: Y is NULL");
+    std::vector<double> cost((size_t)(N > 0 ? N : 0));
+    int rc = lassim_eval_peripheral(h, N, gene, Xp, cost.data(), nullptr);
     if (rc || N == 0) return rc;
-    if (!Y) return fail(h, LASSIM_E_INVALID, "peripheral_trajectories: Y is NULL");
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
     CU(cudaMemcpy(Y, h->d_Y.p, sizeof(double) * (size_t)N * h->T * (h->n + 1),
                   cudaMemcpyDeviceToHost));
     return LASSIM_OK;
@@ -655,7 +676,8 @@ int lassim_last_end_states(lassim_handle *h, int N, double *E) {
     if (!h) return LASSIM_E_INVALID;
     if (!h->last_had_E || N != h->last_N || !E)
         return fail(h, LASSIM_E_STATE, "no knock-down end states for N=%d (last N=%d)", N, h->last_N);
-    CU(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
     CU(cudaDeviceSynchronize());
     CU(cudaMemcpy(E, h->d_E.p, sizeof(double) * (size_t)N * h->K * h->n, cudaMemcpyDeviceToHost));
     return LASSIM_OK;
@@ -665,7 +687,8 @@ int lassim_last_traj_steps(lassim_handle *h, int N, unsigned int *steps) {
     if (!h) return LASSIM_E_INVALID;
     if (N != h->last_N || !steps)
         return fail(h, LASSIM_E_STATE, "no step counts for N=%d (last N=%d)", N, h->last_N);
-    CU(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
     CU(cudaDeviceSynchronize());
     CU(cudaMemcpy(steps, h->d_steps.p, sizeof(unsigned) * (size_t)N * h->K, cudaMemcpyDeviceToHost));
     return LASSIM_OK;
@@ -676,7 +699,8 @@ long long lassim_launch_count(const lassim_handle *h) { return h ? h->launches :
 int lassim_last_kernel_ms(lassim_handle *h, float *ms) {
     if (!h || !ms) return LASSIM_E_INVALID;
     if (!h->timed) return fail(h, LASSIM_E_STATE, "no kernel has been launched yet");
-    CU(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
     CU(cudaEventSynchronize(h->ev1));
     CU(cudaEventElapsedTime(ms, h->ev0, h->ev1));
     return LASSIM_OK;
@@ -684,7 +708,8 @@ int lassim_last_kernel_ms(lassim_handle *h, float *ms) {
 
 int lassim_fp64_peak_probe(lassim_handle *h, int iters, double *tflops) {
     if (!h || !tflops || iters < 1) return LASSIM_E_INVALID;
-    CU(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
     const int blocks = h->sm_count * 8, threads = 256;
     CU(h->d_probe.reserve((size_t)blocks * threads));
     cudaStream_t s = h->stream;
@@ -782,7 +807,8 @@ extern "C" int lassim_eval_device_noalloc(lassim_handle *h, int N, const double 
                     N, L.bytes, (unsigned)LASSIM_NOALLOC_SCRATCH_BYTES,
                     ((size_t)LASSIM_NOALLOC_SCRATCH_BYTES - 2048) / per);
     }
-    CU(cudaSetDevice(h->device));
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
     // one-time set-up on this device: turn the symbol into a device address
     if (!g_noalloc_addr[h->device]) {
         unsigned char *addr = nullptr;
