@@ -9,9 +9,9 @@ the Th2 core problem (12 genes, 63 edges, 6 sample times, 12 knock-down rows ->
 
 One "step" = one pass of the hot path over one population (1024 candidates =
 15,360 trajectories + the fused cost reductions).  With N > 1 (torchrun) every
-rank evaluates its own population of 1024 (islands are independent: weak
-scaling, no data-path collective); `value` = candidates all ranks evaluated /
-max-over-ranks device time.
+rank evaluates its own copy of that population (islands are independent: weak
+scaling with equal work per GPU, no data-path collective); `value` = candidates
+all ranks evaluated / max-over-ranks device time.
 
 Prints ONE JSON line (rank 0).  Keys beyond the base contract:
   roofline      FP64-FMA roofline of the evaluation kernel (the path is
@@ -145,7 +145,7 @@ def run_reference_arm(args):
 def workload_config(n_gpus, l2_note):
     return {"workload": "Th2 core (examples/Th2_lassim_core_TF_network.tsv + data_p1-p4 + "
                         "knock_data): n=12, nnz=63, dim=87, T=6, 15 ODE solves per candidate; "
-                        "DE population 1024 per GPU, uniform in default bounds, default_rng(rank)",
+                        "DE population 1024 per GPU, uniform in default bounds, default_rng(0) on every rank",
             "population_per_gpu": POP, "trajectories_per_candidate": 15,
             "pert_factor": PERT_FACTOR, "rtol": 1.49012e-8, "atol": 1.49012e-8,
             "parallelism": "islands x%d (independent populations, no collective)" % n_gpus,
@@ -212,7 +212,7 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     p = load_th2()
-    X = population(p, rank)
+    X = population(p, 0)      # the config-2 population on every rank: equal work per GPU
     eng = Engine(local)
     eng.set_method(args.method)
     eng.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"], p["pert"], PERT_FACTOR)
