@@ -110,8 +110,8 @@ __device__ __forceinline__ double logistic_libm(double z) {
 // (truncation 4e-17), so the denominator is d = fma(S, f*p, 1 + S): the table
 // value, its exponent scaling and 1 + S depend only on the rounding of t and sit
 // beside the dependent chain  t -> f -> p -> f*p -> d -> 1/d, not on it.  The
-// reciprocal is an SFU seed (MUFU.RCP64H) refined by one third-order FP64 step.
-// ~3 ulp.  |t| >= 1000 (also NaN/inf) selects d = 2^1000 or 1 directly: below
+// reciprocal is an SFU seed (MUFU.RCP64H) refined by one FP64 Newton step
+// (relative error <= 1e-12).  |t| >= 1000 (also NaN/inf) selects d = 2^1000 or 1 directly: below
 // -1000, 2^t vanishes next to 1; above, the result is < 1e-301 where the
 // reference returns vmax*exp(z) or 0 after overflow.  The test runs on the high
 // word with integer ops, in parallel with the chain.
@@ -135,10 +135,10 @@ __device__ __forceinline__ double logistic_fast(double t, const double *tab) {
     if (big) d = (thi < 0) ? 1.0 : 1.0715086071862673e301;   // 2^1000
     double r;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
-    // one third-order step: r*(1 + e0 + e0^2), e0 = 1 - d*r (seed error 2^-23
-    // -> 2^-69), one dependent FMA less than two Newton steps
-    const double e0 = fma(-d, r, 1.0);
-    return fma(r, fma(e0, e0, e0), r);
+    // one Newton step: seed error <= 2^-20 -> <= 2^-40 (1e-12 relative), four
+    // orders below the integration tolerance; a second step would add two
+    // dependent FMAs to every RHS evaluation for digits the error control never sees
+    return fma(r, fma(-d, r, 1.0), r);
 }
 
 // ---------------------------------------------------------------- weights
