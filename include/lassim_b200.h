@@ -90,6 +90,19 @@ int lassim_set_tolerances(lassim_handle *h, double rtol, double atol,
 enum { LASSIM_METHOD_DP45 = 0, LASSIM_METHOD_DOP853 = 1 };
 int lassim_set_method(lassim_handle *h, int method);
 
+/* Speculative step attempts for the time-series trajectories (problems of at
+ * most 16 genes): every attempt is made at the proposed step size and, by the
+ * other half of the warp, at 0.7 of it; when the full step fails its error test
+ * and the shorter one passes, the shorter one is accepted instead of starting
+ * over.  Removes about a fifth of the sequential attempts on trajectories with
+ * many rejections, which is what a small batch waits for; uses twice the lanes
+ * for those trajectories.  0 = off, 1 = on, 2 = automatic (default: on for
+ * batches of at most 2048 candidates).  Results are deterministic for a given
+ * setting and batch-size class, and stay inside the same error control.  (No
+ * reference counterpart.)  LASSIM_SPECULATE in the environment sets the initial
+ * mode. */
+int lassim_set_speculation(lassim_handle *h, int mode);
+
 /* Current decision-vector length (2n + nnz), trajectories per candidate
  * (1 + unique time pairs + n when a knock-down matrix is set, else 1). */
 int lassim_dim(const lassim_handle *h);
@@ -207,7 +220,8 @@ int lassim_eval_device_noalloc(lassim_handle *h, int N, const double *dX,
 long long lassim_flops_per_attempt(const lassim_handle *h);
 const char *lassim_kernel_name(lassim_handle *h);
 
-/* Number of kernels this handle has launched so far. */
+/* Number of kernels this handle has launched so far (an evaluation is one launch,
+ * or two concurrent ones when speculation is active). */
 long long lassim_launch_count(const lassim_handle *h);
 
 /* Device time of the last evaluation kernel in milliseconds (CUDA events on

@@ -51,6 +51,8 @@ def load_library():
     lib.lassim_set_mask.argtypes = [H, c_ubyte_p]
     lib.lassim_set_tolerances.argtypes = [H, ctypes.c_double, ctypes.c_double,
                                           ctypes.c_longlong]
+    lib.lassim_set_speculation.argtypes = [H, ctypes.c_int]
+    lib.lassim_set_speculation.restype = ctypes.c_int
     lib.lassim_set_method.argtypes = [H, ctypes.c_int]
     lib.lassim_set_method.restype = ctypes.c_int
     lib.lassim_dim.argtypes = [H]
@@ -174,6 +176,14 @@ class Engine:
     def set_tolerances(self, rtol=1.49012e-8, atol=1.49012e-8, max_steps=20000000):
         self._check(self._lib.lassim_set_tolerances(self._h, rtol, atol, int(max_steps)),
                     "lassim_set_tolerances")
+
+    def set_speculation(self, mode="auto"):
+        """Speculative half-warp step attempts for time-series trajectories:
+        'off', 'on' or 'auto' (on for batches of at most 2048 candidates)."""
+        code = {"off": 0, "on": 1, "auto": 2, 0: 0, 1: 1, 2: 2, False: 0, True: 1}.get(mode)
+        if code is None:
+            raise ValueError("speculation mode %r (use 'off', 'on' or 'auto')" % (mode,))
+        self._check(self._lib.lassim_set_speculation(self._h, code), "lassim_set_speculation")
 
     def set_method(self, method="dop853"):
         """'dop853' (Dormand-Prince 8(5,3), default) or 'dp45' (Dormand-Prince 5(4))."""

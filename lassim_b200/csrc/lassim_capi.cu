@@ -38,8 +38,9 @@ struct DevBuf {
 struct lassim_handle {
     int device = 0;
     int sm_count = 0;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaStream_t stream = nullptr, stream2 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr;
+    int speculate = 2;        // 0 off, 1 on, 2 auto (small batches)
     bool timed = false;
     std::string err, kernel_name;
     long long launches = 0;
@@ -158,6 +159,7 @@ struct KernelChoice {
     kernel_fn fn;
     int L, R;          // lanes per group, genes per lane
     const char *name;
+    kernel_fn fn_shadow = nullptr;   // warp-per-trajectory speculative variant, if built
 };
 
 // dynamic shared memory of one CTA: header (2^(j/256) table, reduction scratch)
@@ -172,6 +174,13 @@ kernel_fn dense_kernel(int method, bool fast) {
     if (method == kMethodDOP853) return grn_cost_kernel<L, 1, DenseW<1, NC>, kMethodDOP853, true>;
     if (!fast) return grn_cost_kernel<L, 1, DenseW<1, NC>, kMethodDP45, false>;
     return grn_cost_kernel<L, 1, DenseW<1, NC>, kMethodDP45, true>;
+}
+
+template <int NC>
+kernel_fn shadow_kernel(int method) {
+    if (method == kMethodDOP853)
+        return grn_cost_kernel<16, 1, DenseW<1, NC>, kMethodDOP853, true, false, true>;
+    return grn_cost_kernel<16, 1, DenseW<1, NC>, kMethodDP45, true, false, true>;
 }
 
 template <int L>
@@ -207,6 +216,11 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
                      : nc <= 12 ? dense_kernel<16, 12>(method, fast)
                                 : dense_kernel<16, 16>(method, fast);
         *out = {fn, 16, 1, "dense 16x1"};
+        if (fast)
+            out->fn_shadow = nc <= 4 ? shadow_kernel<4>(method)
+                           : nc <= 8 ? shadow_kernel<8>(method)
+                           : nc <= 12 ? shadow_kernel<12>(method)
+                                      : shadow_kernel<16>(method);
         return true;
     }
     if (n <= 32) {
@@ -219,6 +233,61 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
     if (n <= 256) { *out = {sparse_kernel<128>(method, h->max_deg), 128, 2, "sparse 128x2"}; return true; }
     if (n <= 1024) { *out = {sparse_kernel<512>(method, h->max_deg), 512, 2, "sparse 512x2"}; return true; }
     return false;
+}
+
+// Launches the kernel(s) of one evaluation on stream `s`.  `counters` points at two
+// zeroed work-queue counters.  Allocates nothing.
+//
+// Speculative time-series kernel (one warp per trajectory, see grn_kernels.cuh) for
+// batches small enough that the longest trajectory, not throughput, sets the time:
+// the time series go to the speculative kernel on the caller's stream (they are the
+// long ones), the other trajectories run concurrently on the auxiliary stream, and
+// `s` waits for both.
+int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P,
+                   const DevBatch &B, int N, int traj_per_candidate, bool periph,
+                   cudaStream_t s, unsigned int *counters) {
+    const bool speculate = kc.fn_shadow != nullptr && !periph &&
+                           (h->speculate == 1 || (h->speculate == 2 && N <= 2048));
+    const size_t smem = smem_bytes(kc);
+    auto launch = [&](kernel_fn fn, int lanes_per_item, unsigned begin, unsigned count,
+                      unsigned int *counter, cudaStream_t st) -> cudaError_t {
+        if (count == 0) return cudaSuccess;
+        const int threads = threads_for(kc.L);
+        const int items_per_cta = threads / lanes_per_item;
+        cudaError_t e = cudaFuncSetAttribute((const void *)fn,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        int per_sm = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem);
+        if (e != cudaSuccess) return e;
+        if (per_sm < 1) per_sm = 1;
+        long long blocks = ((long long)count + items_per_cta - 1) / items_per_cta;
+        const long long resident = (long long)h->sm_count * per_sm;
+        if (blocks > resident) blocks = resident;
+        if (blocks < 1) blocks = 1;
+        DevBatch Bl = B;
+        Bl.work_begin = begin; Bl.work_count = count; Bl.work_counter = counter;
+        fn<<<(unsigned)blocks, threads, smem, st>>>(P, Bl);
+        h->launches += 1;
+        return cudaGetLastError();
+    };
+    const unsigned total = (unsigned)N * (unsigned)traj_per_candidate;
+    if (speculate) {
+        const unsigned rest = total - (unsigned)N;
+        if (rest > 0) {
+            CU(cudaEventRecord(h->ev_fork, s));
+            CU(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
+        }
+        CU(launch(kc.fn_shadow, 32, 0u, (unsigned)N, counters, s));
+        if (rest > 0) {
+            CU(launch(kc.fn, kc.L, (unsigned)N, rest, counters + 1, h->stream2));
+            CU(cudaEventRecord(h->ev_join, h->stream2));
+            CU(cudaStreamWaitEvent(s, h->ev_join, 0));
+        }
+    } else {
+        CU(launch(kc.fn, kc.L, 0u, total, counters, s));
+    }
+    return LASSIM_OK;
 }
 
 // Peripheral problems integrate n + 1 states (fixed core + one gene) with the
@@ -293,6 +362,7 @@ int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
 
     DevBatch B;
     B.N = N; B.mode = mode; B.X = dX; B.pgene = d_pgene;
+    B.work_begin = 0; B.work_count = 0;     // set per launch below
     B.cost = h->d_cost.p; B.cost_main = h->d_cost_main.p; B.pert_cost = h->d_pert_cost.p;
     B.work_counter = reinterpret_cast<unsigned int *>(h->d_zero.p);
     B.done = reinterpret_cast<int *>(h->d_zero.p + z.off_done);
@@ -300,25 +370,12 @@ int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
     B.counters = reinterpret_cast<unsigned long long *>(h->d_zero.p + z.off_counters);
     B.Y = dY; B.E = h->d_E.p; B.traj_steps = h->d_steps.p; B.order = nullptr;
 
-    const int groups_per_cta = threads_for(kc.L) / kc.L;
-    const size_t smem = smem_bytes(kc);
-    CU(cudaFuncSetAttribute((const void *)kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                            (int)smem));
-    int per_sm = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kc.fn, threads_for(kc.L), smem));
-    if (per_sm < 1) per_sm = 1;
-    const long long work = (long long)N * (mode == 0 ? K : 1);
-    long long blocks = (work + groups_per_cta - 1) / groups_per_cta;
-    const long long resident = (long long)h->sm_count * per_sm;
-    if (blocks > resident) blocks = resident;
-    if (blocks < 1) blocks = 1;
-
     CU(cudaEventRecord(h->ev0, s));
-    kc.fn<<<(unsigned)blocks, threads_for(kc.L), smem, s>>>(P, B);
-    CU(cudaGetLastError());
+    int rc = launch_kernels(h, kc, P, B, N, mode == 0 ? K : 1, periph, s,
+                            reinterpret_cast<unsigned int *>(h->d_zero.p));
+    if (rc) return rc;
     CU(cudaEventRecord(h->ev1, s));
     h->timed = true;
-    h->launches += 1;
     h->last_N = N;
     h->last_had_E = (K > 1 && mode == 0);
     return LASSIM_OK;
@@ -360,10 +417,14 @@ int lassim_create(int device, lassim_handle **out) {
     h->device = device;
     h->sm_count = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess) {
+        cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) != cudaSuccess) {
         delete h;
         return fail(nullptr, LASSIM_E_CUDA, "stream/event creation failed");
     }
+    if (const char *sp = getenv("LASSIM_SPECULATE")) h->speculate = atoi(sp);
     double tab[kExpTable];
     for (int j = 0; j < kExpTable; ++j) tab[j] = exp2((double)j / (double)kExpTable);
     if (cudaMemcpyToSymbol(c_exp2_table, tab, sizeof(tab)) != cudaSuccess) {
@@ -378,6 +439,7 @@ int lassim_destroy(lassim_handle *h) {
     if (!h) return LASSIM_OK;
     DeviceGuard guard_(h->device);
     cudaStreamSynchronize(h->stream);
+    cudaStreamSynchronize(h->stream2);
     h->d_times.release(); h->d_y0.release(); h->d_data.release(); h->d_sigma2.release();
     h->d_pert.release(); h->d_traj_tt.release(); h->d_kidx.release();
     h->d_row_ptr.release(); h->d_col_idx.release();
@@ -388,6 +450,8 @@ int lassim_destroy(lassim_handle *h) {
     h->d_pert_cost.release(); h->d_Y.release(); h->d_E.release(); h->d_probe.release();
     h->d_zero.release(); h->d_steps.release();
     cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
+    cudaEventDestroy(h->ev_fork); cudaEventDestroy(h->ev_join);
+    cudaStreamDestroy(h->stream2);
     cudaStreamDestroy(h->stream);
     delete h;
     return LASSIM_OK;
@@ -486,6 +550,14 @@ int lassim_set_tolerances(lassim_handle *h, double rtol, double atol, long long 
         return fail(h, LASSIM_E_INVALID, "tolerances must be positive (rtol=%g atol=%g max_steps=%lld)",
                     rtol, atol, max_steps);
     h->rtol = rtol; h->atol = atol; h->max_steps = max_steps;
+    return LASSIM_OK;
+}
+
+int lassim_set_speculation(lassim_handle *h, int mode) {
+    if (!h) return LASSIM_E_INVALID;
+    if (mode < 0 || mode > 2)
+        return fail(h, LASSIM_E_INVALID, "speculation mode %d (0 off, 1 on, 2 auto)", mode);
+    h->speculate = mode;
     return LASSIM_OK;
 }
 
@@ -841,6 +913,7 @@ extern "C" int lassim_eval_device_noalloc(lassim_handle *h, int N, const double 
 
     DevBatch B;
     B.N = N; B.mode = 0; B.X = dX; B.pgene = nullptr;
+    B.work_begin = 0; B.work_count = (unsigned)N * (unsigned)K;
     B.cost = dcost;                                           // straight into the caller's buffer
     B.work_counter = reinterpret_cast<unsigned int *>(base);
     B.done = reinterpret_cast<int *>(base + L.off_done);
@@ -853,20 +926,9 @@ extern "C" int lassim_eval_device_noalloc(lassim_handle *h, int N, const double 
     B.E = reinterpret_cast<double *>(base + L.off_E);
     B.order = nullptr;
 
-    const int groups_per_cta = threads_for(kc.L) / kc.L;
-    const size_t smem = smem_bytes(kc);
-    CU(cudaFuncSetAttribute((const void *)kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                            (int)smem));
-    int per_sm = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kc.fn, threads_for(kc.L), smem));
-    if (per_sm < 1) per_sm = 1;
-    const long long work = (long long)N * K;
-    long long blocks = (work + groups_per_cta - 1) / groups_per_cta;
-    const long long resident = (long long)h->sm_count * per_sm;
-    if (blocks > resident) blocks = resident;
-    kc.fn<<<(unsigned)blocks, threads_for(kc.L), smem, s>>>(P, B);
-    CU(cudaGetLastError());
-    h->launches += 1;
+    // same kernels, same speculation policy as lassim_eval_device: same costs
+    int rc = launch_kernels(h, kc, P, B, N, K, false, s, reinterpret_cast<unsigned int *>(base));
+    if (rc) return rc;
     return LASSIM_OK;
 }
 

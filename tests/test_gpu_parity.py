@@ -442,6 +442,34 @@ def test_argument_errors(engine, th2):
     bind_th2(engine, th2)
 
 
+def test_speculative_attempts_stay_inside_the_error_control(engine, th2, th2_uniform):
+    """Time-series trajectories of small batches run with a second, shorter step
+    attempt in the other half of the warp (lassim_set_speculation).  On, off and
+    auto must all pass the parity gate; on and off differ only at the level of
+    the integration tolerance; each setting is deterministic."""
+    g = th2_uniform
+    bind_th2(engine, th2)
+    well = rel(g["ref_cost_main"], g["tight_cost_main"]) <= 1e-7
+    res = {}
+    for mode in ("off", "on", "auto"):
+        engine.set_speculation(mode)
+        a = engine.eval(g["X"], details=True)
+        b = engine.eval(g["X"], details=True)
+        np.testing.assert_array_equal(a["cost"], b["cost"])
+        assert (a["status"] == 0).all()
+        assert rel(a["cost_main"], g["ref_cost_main"])[well].max() <= COST_RTOL
+        res[mode] = a
+    np.testing.assert_array_equal(res["on"]["cost"], res["auto"]["cost"])     # 128 <= 2048
+    assert rel(res["on"]["cost_main"], res["off"]["cost_main"])[well].max() <= COST_RTOL
+    # fewer sequential attempts on the time series with speculation
+    engine.set_speculation("off"); engine.eval(g["X"]); off = engine.last_traj_steps(128)[:, 0]
+    engine.set_speculation("on"); engine.eval(g["X"]); on = engine.last_traj_steps(128)[:, 0]
+    assert on.max() < off.max() and on.sum() < off.sum()
+    with pytest.raises(ValueError):
+        engine.set_speculation("maybe")
+    engine.set_speculation("auto")
+
+
 def test_exact_math_variant_agrees(th2, th2_uniform):
     """libm exp + IEEE division (LASSIM_EXACT_MATH=1) vs the exp2/Newton
     logistic: same costs to far below the integration tolerance."""
