@@ -50,23 +50,27 @@ class de:
         ub = np.asarray(pop.problem.ub, dtype=np.float64)
         best = X[pop.best_idx()]
         # five mutually distinct partners, all different from i
-        R = np.empty((NP, 5), dtype=np.int64)
-        for i in range(NP):
-            choices = rng.choice(NP - 1, size=5, replace=False)
-            R[i] = choices + (choices >= i)
-        r1, r2, r3, r4, r5 = (X[R[:, j]] for j in range(5))
+        # (the five smallest of NP - 1 uniform keys per row = a uniform draw
+        # without replacement; indices >= i are shifted past i)
+        keys = rng.random((NP, NP - 1), dtype=np.float32)
+        R = np.argpartition(keys, 4, axis=1)[:, :5]
+        R = R + (R >= np.arange(NP)[:, None])
+
+        def partner(j):      # gathered only when the variant uses it
+            return X[R[:, j]]
+
         F = self.f
         kind = (self.variant - 1) % 5
         if kind == 0:      # best/1
-            mutant = best + F * (r2 - r3)
+            mutant = best + F * (partner(1) - partner(2))
         elif kind == 1:    # rand/1
-            mutant = r1 + F * (r2 - r3)
+            mutant = partner(0) + F * (partner(1) - partner(2))
         elif kind == 2:    # rand-to-best/1
-            mutant = X + F * (best - X) + F * (r1 - r2)
+            mutant = X + F * (best - X) + F * (partner(0) - partner(1))
         elif kind == 3:    # best/2
-            mutant = best + F * (r1 + r2 - r3 - r4)
+            mutant = best + F * (partner(0) + partner(1) - partner(2) - partner(3))
         else:              # rand/2
-            mutant = r5 + F * (r1 + r2 - r3 - r4)
+            mutant = partner(4) + F * (partner(0) + partner(1) - partner(2) - partner(3))
         if self.variant <= 5:
             # exponential crossover: a run of consecutive components starting
             # at a random index, continued while rand < CR (at least one)
