@@ -50,10 +50,15 @@ class de:
         ub = np.asarray(pop.problem.ub, dtype=np.float64)
         best = X[pop.best_idx()]
         # five mutually distinct partners, all different from i
-        # (the five smallest of NP - 1 uniform keys per row = a uniform draw
-        # without replacement; indices >= i are shifted past i)
-        keys = rng.random((NP, NP - 1), dtype=np.float32)
-        R = np.argpartition(keys, 4, axis=1)[:, :5]
+        # (draw with replacement, redraw the few rows that repeat a value;
+        # indices >= i are then shifted past i)
+        R = rng.integers(0, NP - 1, size=(NP, 5))
+        while True:
+            srt = np.sort(R, axis=1)
+            bad = np.flatnonzero((srt[:, 1:] == srt[:, :-1]).any(axis=1))
+            if bad.size == 0:
+                break
+            R[bad] = rng.integers(0, NP - 1, size=(bad.size, 5))
         R = R + (R >= np.arange(NP)[:, None])
 
         def partner(j):      # gathered only when the variant uses it
