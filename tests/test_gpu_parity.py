@@ -375,6 +375,52 @@ def test_synthetic_200_gene_golden(engine):
     assert err[well].max() <= (TRAJ_RTOL if engine.method_name == "dop853" else 3e-5)
 
 
+def test_degenerate_and_extreme_parameters(engine, th2, th2_late):
+    """Corners of the parameter box and beyond: no degradation, no production,
+    no regulation; logistic terms saturated for good (the reference relies on exp
+    overflow -> +inf -> term 0, common_functions.pyx:37-39), where the system has
+    a closed-form solution; non-finite input."""
+    p = th2
+    bind_th2(engine, p, pert=False)
+    base = th2_late["X"][0].copy()
+    cases = {}
+    x = base.copy(); x[:12] = 0.0; cases["lambda = 0"] = x
+    x = base.copy(); x[12:24] = 0.0; cases["vmax = 0"] = x
+    x = base.copy(); x[24:] = 0.0; cases["k = 0"] = x
+    X = np.array(list(cases.values()))
+    out = engine.eval(X, details=True)
+    assert (out["status"] == 0).all()
+    for name, x, got in zip(cases, X, out["cost_main"]):
+        want = orc.core_cost(x, p["data"], p["sigma"], p["times"], p["y0"], p["vector_map"],
+                             p["mask"], orc.tight_ode())
+        assert got == pytest.approx(want, rel=COST_RTOL), name
+    # k = -1e6: every argument is <= -1e5, exp(-z) overflows, production is 0:
+    #   y(t) = y0 exp(-lambda t).   k = +1e6: sigmoid = 1:  y -> vmax/lambda.
+    lam = np.linspace(0.001, 0.01, 12)      # slow decay: the regulators stay O(1) up to t = 192
+    vmax = np.linspace(0.3, 1.4, 12)
+    t = p["times"][:, None]
+    off = np.concatenate([lam, vmax, np.full(63, -1.0e6)])
+    on = np.concatenate([lam, vmax, np.full(63, 1.0e6)])
+    Y = engine.trajectories(np.array([off, on]))
+    np.testing.assert_allclose(Y[0], p["y0"] * np.exp(-lam * t), rtol=1e-6, atol=1e-9)
+    np.testing.assert_allclose(Y[1], vmax / lam + (p["y0"] - vmax / lam) * np.exp(-lam * t),
+                               rtol=1e-6, atol=1e-9)
+    bad = np.array([base, base, base])
+    bad[0, 3] = np.nan          # a degradation rate
+    bad[1, 5] = np.inf
+    bad[2, 15] = -np.inf        # a vmax
+    out = engine.eval(bad, details=True)
+    assert (out["status"] != 0).all() and not np.isfinite(out["cost"]).any()
+    # an infinite WEIGHT is not an error: the term saturates, as in the reference
+    # (exp(-inf) = 0 -> vmax / 1)
+    sat = base.copy(); sat[30] = np.inf
+    big = base.copy(); big[30] = 1.0e12
+    o = engine.eval(np.array([sat, big]), details=True)
+    assert (o["status"] == 0).all() and o["cost_main"][0] == pytest.approx(o["cost_main"][1], rel=1e-9)
+    # and the engine is fine afterwards
+    assert np.isfinite(engine.eval(base)).all()
+
+
 def test_empty_and_single_batches(engine, th2, th2_uniform):
     bind_th2(engine, th2)
     assert engine.eval(np.empty((0, 87))).shape == (0,)
