@@ -166,6 +166,38 @@ int lassim_peripheral_trajectories(lassim_handle *h, int N, const int *gene,
                                    const double *Xp, double *Y);
 
 /*
+ * Differential evolution on the device.  PyGMO's DE calls the objective once per
+ * individual from C++ into Python (the archipelago of
+ * source/core/base_optimization.py:159-203 drives it); here the populations of
+ * all islands of this GPU live in device memory and one evolve round runs
+ * `generations` x (trial vectors -> evaluation -> greedy selection) on the
+ * handle's stream without a host round trip.  Semantics as pagmo 1.x `de`:
+ * variants 1-10, generation-synchronous, out-of-box components re-drawn
+ * uniformly, a trial wins only if strictly better, failed integrations cost +inf,
+ * NaN never wins.
+ *   lassim_de_init   X0[islands*individuals*dim] initial populations (host),
+ *                    lb/ub[dim], individuals >= 6, f and cr in [0,1]
+ *   lassim_de_evolve enqueues; lassim_de_get / _best synchronise
+ *   lassim_de_best   table[islands*(dim+1)]: rows (x | f) of every island's best
+ *   lassim_de_migrate_ring  PyGMO's default policy on a ring: each of this GPU's
+ *                    islands (island j is row first_island + j*stride of a table of
+ *                    n_table islands gathered by the caller across GPUs; islands
+ *                    are dealt round-robin to ranks) takes its two neighbours'
+ *                    bests, each replacing the island's worst if strictly better
+ *   lassim_de_set_individual  seed one individual (e.g. a known solution)
+ */
+int lassim_de_init(lassim_handle *h, int islands, int individuals, int variant, double f,
+                   double cr, unsigned long long seed, const double *lb, const double *ub,
+                   const double *X0);
+int lassim_de_set_individual(lassim_handle *h, int island, int index, const double *x);
+int lassim_de_evolve(lassim_handle *h, int generations);
+int lassim_de_best(lassim_handle *h, double *table);
+int lassim_de_migrate_ring(lassim_handle *h, const double *table, int n_table, int first_island,
+                           int stride);
+int lassim_de_get(lassim_handle *h, double *X, double *F);
+long long lassim_de_evaluations(const lassim_handle *h);
+
+/*
  * End states of the knock-down part of the LAST lassim_eval / _eval_device
  * call: E[N*K*n], K = lassim_trajectories_per_candidate(); slot 0 is unused
  * (time series), 1..U the controls in order of first appearance, 1+U+i the

@@ -77,6 +77,19 @@ def load_library():
     for name in ("lassim_set_peripheral", "lassim_eval_peripheral",
                  "lassim_peripheral_trajectories"):
         getattr(lib, name).restype = ctypes.c_int
+    lib.lassim_de_init.argtypes = [H, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_double,
+                                   ctypes.c_double, ctypes.c_ulonglong, c_double_p, c_double_p,
+                                   c_double_p]
+    lib.lassim_de_set_individual.argtypes = [H, ctypes.c_int, ctypes.c_int, c_double_p]
+    lib.lassim_de_evolve.argtypes = [H, ctypes.c_int]
+    lib.lassim_de_best.argtypes = [H, c_double_p]
+    lib.lassim_de_migrate_ring.argtypes = [H, c_double_p, ctypes.c_int, ctypes.c_int, ctypes.c_int]
+    lib.lassim_de_get.argtypes = [H, c_double_p, c_double_p]
+    lib.lassim_de_evaluations.argtypes = [H]
+    lib.lassim_de_evaluations.restype = ctypes.c_longlong
+    for name in ("lassim_de_init", "lassim_de_set_individual", "lassim_de_evolve",
+                 "lassim_de_best", "lassim_de_migrate_ring", "lassim_de_get"):
+        getattr(lib, name).restype = ctypes.c_int
     lib.lassim_last_end_states.argtypes = [H, ctypes.c_int, c_double_p]
     lib.lassim_last_traj_steps.argtypes = [H, ctypes.c_int, c_uint_p]
     lib.lassim_flops_per_attempt.argtypes = [H]
@@ -315,6 +328,53 @@ class Engine:
             self._h, N, gene.ctypes.data_as(c_int_p), _dp(Xp), _dp(Y)),
             "lassim_peripheral_trajectories")
         return Y
+
+    # -- differential evolution on the device ------------------------------
+    def de_init(self, X0, lb, ub, variant=2, f=0.8, cr=0.9, seed=0):
+        """X0[islands, individuals, dim]: initial populations of this GPU's islands."""
+        X0 = _f64(X0)
+        if X0.ndim != 3 or X0.shape[2] != self.dim:
+            raise ValueError("populations of shape %s, expected (islands, individuals, %d)"
+                             % (X0.shape, self.dim))
+        lb = _f64(lb).reshape(-1); ub = _f64(ub).reshape(-1)
+        if lb.size != self.dim or ub.size != self.dim:
+            raise ValueError("bounds of length %d/%d for dimension %d" % (lb.size, ub.size, self.dim))
+        self._check(self._lib.lassim_de_init(self._h, X0.shape[0], X0.shape[1], int(variant),
+                                             float(f), float(cr), int(seed) & (2 ** 64 - 1),
+                                             _dp(lb), _dp(ub), _dp(X0)), "lassim_de_init")
+        self._de_shape = X0.shape
+
+    def de_set_individual(self, island, index, x):
+        x = _f64(x).reshape(-1)
+        if x.size != self.dim:
+            raise ValueError("individual of length %d for dimension %d" % (x.size, self.dim))
+        self._check(self._lib.lassim_de_set_individual(self._h, int(island), int(index), _dp(x)),
+                    "lassim_de_set_individual")
+
+    def de_evolve(self, generations):
+        self._check(self._lib.lassim_de_evolve(self._h, int(generations)), "lassim_de_evolve")
+
+    def de_best(self):
+        I, _, D = self._de_shape
+        table = np.empty((I, D + 1))
+        self._check(self._lib.lassim_de_best(self._h, _dp(table)), "lassim_de_best")
+        return table
+
+    def de_migrate_ring(self, table, first_island=0, stride=1):
+        table = _f64(table)
+        self._check(self._lib.lassim_de_migrate_ring(self._h, _dp(table), table.shape[0],
+                                                     int(first_island), int(stride)),
+                    "lassim_de_migrate_ring")
+
+    def de_get(self):
+        I, NP, D = self._de_shape
+        X = np.empty((I, NP, D)); F = np.empty((I, NP))
+        self._check(self._lib.lassim_de_get(self._h, _dp(X), _dp(F)), "lassim_de_get")
+        return X, F
+
+    @property
+    def de_evaluations(self):
+        return int(self._lib.lassim_de_evaluations(self._h))
 
     def last_end_states(self, N):
         K = self.trajectories_per_candidate

@@ -5,7 +5,9 @@ from inspect import signature
 
 from sortedcontainers import SortedList
 
-from ..pygmo import archipelago, island, topology
+import os
+
+from ..pygmo import archipelago, device_archipelago, island, topology
 
 
 class BaseOptimization:
@@ -26,6 +28,7 @@ class BaseOptimization:
         self._n_islands = 0
         self._n_individuals = 0
         self._seed = None
+        self._device_de = False
         self.evaluations = 0
 
     def build(self, context, prob_factory, start_problem, reactions, handler,
@@ -38,6 +41,10 @@ class BaseOptimization:
         new._handler = handler
         new._logger = logger if logger is not None else logging.getLogger(__name__)
         new._seed = kwargs.get("seed")
+        # device_de=True (or LASSIM_DEVICE_DE=1): populations stay on the GPU and a whole
+        # evolve round runs without a host round trip (pygmo/device_archipelago.py)
+        new._device_de = bool(kwargs.get("device_de",
+                                         os.environ.get("LASSIM_DEVICE_DE", "0") not in ("", "0")))
         opt_args = context.primary_first
         params = self.handle_parameters(opt_args)
         new._algorithm = new._algorithm(**params) if params else new._algorithm()
@@ -93,8 +100,9 @@ class BaseOptimization:
     def _generate_archipelago(self, prob, topol):
         """n_islands - 1 random islands plus one seeded with the problem's
         known champions (:179-203)."""
-        archi = archipelago(self._algorithm, prob, self._n_islands - 1,
-                            self._n_individuals, topology=topol, seed=self._seed)
+        kind = device_archipelago if self._device_de else archipelago
+        archi = kind(self._algorithm, prob, self._n_islands - 1,
+                     self._n_individuals, topology=topol, seed=self._seed)
         isl = island(self._algorithm, prob, self._n_individuals,
                      seed=archi._seed_seq.spawn(1)[0])
         for i, champ in enumerate(prob.champions[:self._n_individuals]):

@@ -4,6 +4,7 @@
 // every evaluation entry point launches a CUDA kernel or fails.
 #include "../../include/lassim_b200.h"
 #include "grn_kernels.cuh"
+#include "de_kernels.cuh"
 
 #include <cmath>
 #include <cstdarg>
@@ -70,6 +71,12 @@ struct lassim_handle {
     DevBuf<unsigned int> d_steps;
     int last_N = 0;
     bool last_had_E = false;
+
+    // on-device differential evolution (lassim_de_*)
+    bool de_ready = false, de_evaluated = false;
+    DeParams de{};
+    long long de_evaluations = 0;
+    DevBuf<double> de_X, de_F, de_trial, de_best, de_table, de_lb, de_ub;
 };
 
 namespace {
@@ -445,6 +452,8 @@ int lassim_destroy(lassim_handle *h) {
     h->d_row_ptr.release(); h->d_col_idx.release();
     h->d_core_x.release(); h->d_pdata.release(); h->d_psigma2.release(); h->d_py0.release();
     h->d_pmask.release(); h->d_pgene.release();
+    h->de_X.release(); h->de_F.release(); h->de_trial.release(); h->de_best.release();
+    h->de_table.release(); h->de_lb.release(); h->de_ub.release();
     h->d_traj_prefix.release(); h->d_knock_ctrl.release();
     h->d_X.release(); h->d_cost.release(); h->d_cost_main.release();
     h->d_pert_cost.release(); h->d_Y.release(); h->d_E.release(); h->d_probe.release();
@@ -481,6 +490,7 @@ int lassim_set_problem(lassim_handle *h, int n, int T, const double *times,
     CU(guard_.err);
     h->has_problem = false;
     h->p_genes = 0;
+    h->de_ready = false;
     h->n = n; h->T = T; h->pert_factor = pert_factor;
     std::vector<double> sigma2(n);
     for (int i = 0; i < n; ++i) sigma2[i] = sigma[i] * sigma[i];
@@ -806,6 +816,168 @@ int lassim_fp64_peak_probe(lassim_handle *h, int iters, double *tflops) {
 }
 
 }  // extern "C"
+
+
+// ---------------------------------------------------------------------------
+// Differential evolution on the device (de_kernels.cuh): the populations of all
+// islands of this GPU stay in HBM; one evolve round is `gen` x (trial kernel ->
+// evaluation kernel(s) -> selection kernel) on the handle's stream, no host
+// round trip.  Replaces the per-individual objfun callbacks of PyGMO's DE
+// (source/core/base_optimization.py:173-174 drives them).
+// ---------------------------------------------------------------------------
+namespace {
+
+int de_evaluate_population(lassim_handle *h) {
+    const int count = h->de.islands * h->de.np;
+    cudaStream_t s = h->stream;
+    int rc = launch_eval(h, count, 0, h->de_X.p, nullptr, s);
+    if (rc) return rc;
+    const ZeroLayout z = zero_layout(count);
+    de_mask_status_kernel<<<(count + 255) / 256, 256, 0, s>>>(
+        count, reinterpret_cast<const int *>(h->d_zero.p + z.off_status), h->d_cost.p);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(h->de_F.p, h->d_cost.p, sizeof(double) * (size_t)count,
+                       cudaMemcpyDeviceToDevice, s));
+    h->launches += 1;
+    h->de_evaluations += count;
+    h->de_evaluated = true;
+    return LASSIM_OK;
+}
+
+}  // namespace
+
+extern "C" int lassim_de_init(lassim_handle *h, int islands, int individuals, int variant,
+                              double f, double cr, unsigned long long seed, const double *lb,
+                              const double *ub, const double *X0) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->has_problem) return fail(h, LASSIM_E_STATE, "de_init before set_problem");
+    if (islands < 1 || individuals < 6 || variant < 1 || variant > 10 || !lb || !ub || !X0 ||
+        !(f >= 0.0 && f <= 1.0) || !(cr >= 0.0 && cr <= 1.0))
+        return fail(h, LASSIM_E_INVALID,
+                    "de_init: islands=%d individuals=%d (>= 6) variant=%d (1..10) f=%g cr=%g "
+                    "(both in [0,1]) or a NULL array", islands, individuals, variant, f, cr);
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
+    const size_t dim = (size_t)h->dim, count = (size_t)islands * individuals;
+    CU(h->de_X.reserve(count * dim));
+    CU(h->de_trial.reserve(count * dim));
+    CU(h->de_F.reserve(count));
+    CU(h->de_best.reserve((size_t)islands * (dim + 1)));
+    int rc;
+    if ((rc = upload(h, h->de_lb, lb, dim))) return rc;
+    if ((rc = upload(h, h->de_ub, ub, dim))) return rc;
+    CU(cudaMemcpyAsync(h->de_X.p, X0, sizeof(double) * count * dim, cudaMemcpyHostToDevice,
+                       h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    h->de = DeParams{islands, individuals, (int)dim, variant, f, cr, seed, 0ull};
+    h->de_ready = true;
+    h->de_evaluated = false;
+    h->de_evaluations = 0;
+    return LASSIM_OK;
+}
+
+extern "C" int lassim_de_set_individual(lassim_handle *h, int island, int index, const double *x) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->de_ready) return fail(h, LASSIM_E_STATE, "de_set_individual before de_init");
+    if (island < 0 || island >= h->de.islands || index < 0 || index >= h->de.np || !x)
+        return fail(h, LASSIM_E_INVALID, "de_set_individual: island %d index %d", island, index);
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
+    CU(cudaMemcpyAsync(h->de_X.p + ((size_t)island * h->de.np + index) * h->de.dim, x,
+                       sizeof(double) * h->de.dim, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    h->de_evaluated = false;          // the whole population is re-evaluated next time
+    return LASSIM_OK;
+}
+
+extern "C" int lassim_de_evolve(lassim_handle *h, int generations) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->de_ready) return fail(h, LASSIM_E_STATE, "de_evolve before de_init");
+    if (h->de.dim != h->dim)
+        return fail(h, LASSIM_E_STATE, "the problem dimension changed since de_init (%d -> %d)",
+                    h->de.dim, h->dim);
+    if (generations < 0) return fail(h, LASSIM_E_INVALID, "de_evolve: generations=%d", generations);
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
+    cudaStream_t s = h->stream;
+    const int count = h->de.islands * h->de.np;
+    const int blocks = (count + 127) / 128;
+    int rc;
+    if (!h->de_evaluated && (rc = de_evaluate_population(h))) return rc;
+    for (int g = 0; g < generations; ++g) {
+        de_trial_kernel<<<blocks, 128, 0, s>>>(h->de, h->de_X.p, h->de_F.p, h->de_lb.p,
+                                                h->de_ub.p, h->de_trial.p);
+        CU(cudaGetLastError());
+        if ((rc = launch_eval(h, count, 0, h->de_trial.p, nullptr, s))) return rc;
+        const ZeroLayout z = zero_layout(count);
+        de_mask_status_kernel<<<(count + 255) / 256, 256, 0, s>>>(
+            count, reinterpret_cast<const int *>(h->d_zero.p + z.off_status), h->d_cost.p);
+        de_select_kernel<<<blocks, 128, 0, s>>>(h->de, h->de_X.p, h->de_F.p, h->de_trial.p,
+                                                 h->d_cost.p);
+        CU(cudaGetLastError());
+        h->launches += 3;
+        h->de.generation += 1;
+        h->de_evaluations += count;
+    }
+    return LASSIM_OK;       // enqueued; lassim_de_get / lassim_de_best synchronise
+}
+
+extern "C" int lassim_de_best(lassim_handle *h, double *table) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->de_ready || !table) return fail(h, LASSIM_E_STATE, "de_best before de_init / NULL");
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
+    int rc;
+    if (!h->de_evaluated && (rc = de_evaluate_population(h))) return rc;
+    de_best_kernel<<<h->de.islands, 32, 0, h->stream>>>(h->de, h->de_X.p, h->de_F.p, h->de_best.p);
+    CU(cudaGetLastError());
+    h->launches += 1;
+    CU(cudaMemcpyAsync(table, h->de_best.p, sizeof(double) * (size_t)h->de.islands * (h->de.dim + 1),
+                       cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return LASSIM_OK;
+}
+
+extern "C" int lassim_de_migrate_ring(lassim_handle *h, const double *table, int n_table,
+                                      int first_island, int stride) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->de_ready || !table) return fail(h, LASSIM_E_STATE, "de_migrate before de_init / NULL");
+    if (stride < 1 || first_island < 0 ||
+        first_island + (h->de.islands - 1) * stride >= n_table)
+        return fail(h, LASSIM_E_INVALID,
+                    "de_migrate: table of %d islands, mine are %d from %d with stride %d",
+                    n_table, h->de.islands, first_island, stride);
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
+    int rc;
+    if ((rc = upload(h, h->de_table, table, (size_t)n_table * (h->de.dim + 1)))) return rc;
+    de_migrate_ring_kernel<<<h->de.islands, 32, 0, h->stream>>>(h->de, h->de_X.p, h->de_F.p,
+                                                                h->de_table.p, n_table, first_island, stride);
+    CU(cudaGetLastError());
+    h->launches += 1;
+    CU(cudaStreamSynchronize(h->stream));      // `table` is the caller's
+    return LASSIM_OK;
+}
+
+extern "C" int lassim_de_get(lassim_handle *h, double *X, double *F) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->de_ready) return fail(h, LASSIM_E_STATE, "de_get before de_init");
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
+    int rc;
+    if (!h->de_evaluated && (rc = de_evaluate_population(h))) return rc;
+    const size_t count = (size_t)h->de.islands * h->de.np;
+    if (X) CU(cudaMemcpyAsync(X, h->de_X.p, sizeof(double) * count * h->de.dim,
+                              cudaMemcpyDeviceToHost, h->stream));
+    if (F) CU(cudaMemcpyAsync(F, h->de_F.p, sizeof(double) * count, cudaMemcpyDeviceToHost,
+                              h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return LASSIM_OK;
+}
+
+extern "C" long long lassim_de_evaluations(const lassim_handle *h) {
+    return h ? h->de_evaluations : -1;
+}
 
 // ---------------------------------------------------------------------------
 // Evaluation without any allocation.

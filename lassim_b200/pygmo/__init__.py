@@ -8,3 +8,4 @@ from . import algorithm, core, problem, topology  # noqa: F401
 from .core import champion  # noqa: F401
 from .population import population  # noqa: F401
 from .archipelago import archipelago, island  # noqa: F401
+from .device_archipelago import device_archipelago  # noqa: F401

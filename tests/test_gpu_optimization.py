@@ -98,3 +98,19 @@ def test_de_improves_the_th2_fit(th2, tmp_path):
     best = opt.solve(topol=topology.ring())[0]
     assert best.cost < start_best          # 12 generations of DE beat a random draw of 32
     assert opt.evaluations == 2 * 16 * (1 + 12)
+
+
+def test_solve_with_populations_on_the_device(th2, tmp_path):
+    from lassim_b200.pygmo import topology
+    core, context, data, factory, builder, problem = build(
+        th2, tmp_path, islands=2, individuals=16, evolutions=3, gen=4)
+    builder._iterate = None
+    handler = Collect()
+    opt = builder.build(context, factory, problem, SortedDict(core.from_reactions_to_ids()),
+                        handler, logging.getLogger("test"), seed=9, device_de=True)
+    start = np.random.default_rng(0).uniform(problem.lb, problem.ub, size=(32, 87))
+    best = opt.solve(topol=topology.ring())[0]
+    assert best.cost < np.percentile(problem.objfun_batch(start), 10)   # 12 generations of DE
+    assert opt.evaluations == 2 * 16 * (1 + 12)
+    again = problem.objfun_batch(best.solution_vector[None, :])[0]
+    assert again == pytest.approx(best.cost, rel=1e-12)
