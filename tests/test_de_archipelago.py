@@ -133,3 +133,36 @@ def test_two_rank_gloo_islands(tmp_path):
     # both ranks end with the same view of all four islands' champions
     np.testing.assert_array_equal(f0, f1)
     assert f0.shape == (4,) and np.isfinite(f0).all()
+
+
+SHARD_SCRIPT = r"""
+import os, sys
+import numpy as np
+import torch.distributed as dist
+sys.path.insert(0, {repo!r})
+from lassim_b200.core.peripheral_problem import PeripheralSweep
+dist.init_process_group("gloo")
+
+
+class FakeCore:            # local_genes() only needs the sizes
+    _size = 3
+
+
+sweep = PeripheralSweep(FakeCore(), np.zeros(9), np.zeros((11, 4)), 0.2, np.zeros(11))
+mine = sweep.local_genes()
+np.save(os.path.join({out!r}, "genes_%d.npy" % dist.get_rank()), mine)
+dist.destroy_process_group()
+"""
+
+
+def test_peripheral_genes_shard_by_rank(tmp_path):
+    script = tmp_path / "shard.py"
+    script.write_text(SHARD_SCRIPT.format(repo=REPO, out=str(tmp_path)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+           "--nproc-per-node=2", "--master-addr", "127.0.0.1", "--master-port",
+           "29533", str(script)]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    g0 = np.load(tmp_path / "genes_0.npy")
+    g1 = np.load(tmp_path / "genes_1.npy")
+    assert g0.tolist() == [0, 2, 4, 6, 8, 10] and g1.tolist() == [1, 3, 5, 7, 9]
