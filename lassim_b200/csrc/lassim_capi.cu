@@ -213,8 +213,11 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
     const char *ex = getenv("LASSIM_EXACT_MATH");
     const bool fast = !(ex && atoi(ex) != 0);
     const int nc = (n + 3) & ~3;
-    if (n <= 12 && want == 4 && method == kMethodDP45) {
-        *out = {grn_cost_kernel<4, 3, DenseW<3, 12>, kMethodDP45, true>, 4, 3, "dense 4x3"};
+    if (n <= 12 && want == 4) {
+        if (method == kMethodDP45)
+            *out = {grn_cost_kernel<4, 3, DenseW<3, 12>, kMethodDP45, true>, 4, 3, "dense 4x3"};
+        else
+            *out = {grn_cost_kernel<4, 3, DenseW<3, 12>, kMethodDOP853, true>, 4, 3, "dense 4x3"};
         return true;
     }
     if (n <= 16) {
