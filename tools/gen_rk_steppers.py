@@ -102,6 +102,7 @@ def emit(tb):
         w("    }")
     # last evaluation f(yn) and the error estimates
     nE = len(E)
+    early = all(E[m][S] == 0.0 for m in range(nE))     # the estimate does not need f(yn)
     w("    // f(yn) (first stage of the next step) and the error estimate%s" % ("s" if nE > 1 else ""))
     w("    double isc[R];")
     for m in range(nE):
@@ -118,25 +119,39 @@ def emit(tb):
         else:
             w("        ce%d[r] = 0.0;" % m)
             w("        eq%d[r] = %s;" % (m, base))
-    w("        // error weight rtol*max(|y|,|yn|) + atol: needs y and yn only, off the critical path")
-    w("        isc[r] = 1.0 / fma(rtol, fmax(fabs(y[r]), fabs(yn[r])), atol);")
+    w("        // error weight rtol*max(|y|,|yn|) + atol; its reciprocal to 1e-12 is plenty for a")
+    w("        // step-size decision and keeps an IEEE division off the path")
+    w("        isc[r] = fast_rcp(fma(rtol, fmax(fabs(y[r]), fabs(yn[r])), atol));")
     w("    }")
-    w("    sig(yn, sg);")
-    for m in range(nE):
-        w("    double qd%d = 0.0;" % m)
-    w("#pragma unroll")
-    w("    for (int r = 0; r < R; ++r) {")
-    w("        kn[r] = fma(vm[r], sg[r], ly[r]);")
-    for m in range(nE):
-        if E[m][S] != 0.0:
-            w("        const double e%d = fma(ce%d[r], sg[r], eq%d[r]);" % (m, m, m))
-        else:
-            w("        const double e%d = eq%d[r];" % (m, m))
-        w("        qd%d = fmax(qd%d, fabs(e%d) * isc[r]);      // fmax drops NaN: checked next" % (m, m, m))
-        w("        if (e%d != e%d) qd%d = CUDART_INF;" % (m, m, m))
-    w("    }")
-    for m in range(nE):
-        w("    const float n%d = gmax((qd%d <= 3.0e38) ? (float)qd%d : CUDART_INF_F);" % (m, m, m))
+
+    def emit_measure():
+        for m in range(nE):
+            w("    double qd%d = 0.0;" % m)
+        w("#pragma unroll")
+        w("    for (int r = 0; r < R; ++r) {")
+        for m in range(nE):
+            if E[m][S] != 0.0:
+                w("        const double e%d = fma(ce%d[r], sg[r], eq%d[r]);" % (m, m, m))
+            else:
+                w("        const double e%d = eq%d[r];" % (m, m))
+            w("        qd%d = fmax(qd%d, fabs(e%d) * isc[r]);      // fmax drops NaN: checked next" % (m, m, m))
+            w("        if (e%d != e%d) qd%d = CUDART_INF;" % (m, m, m))
+        w("    }")
+        for m in range(nE):
+            w("    const float n%d = gmax((qd%d <= 3.0e38) ? (float)qd%d : CUDART_INF_F);" % (m, m, m))
+
+    if early:
+        w("    // the estimate needs k1..k%d only: reduce it over the group BEFORE f(yn), so that the" % S)
+        w("    // shuffles of the reduction overlap the dependent chain of that last evaluation")
+        emit_measure()
+        w("    sig(yn, sg);")
+        w("#pragma unroll")
+        w("    for (int r = 0; r < R; ++r) kn[r] = fma(vm[r], sg[r], ly[r]);")
+    else:
+        w("    sig(yn, sg);")
+        w("#pragma unroll")
+        w("    for (int r = 0; r < R; ++r) kn[r] = fma(vm[r], sg[r], ly[r]);")
+        emit_measure()
     if nE == 1:
         w("    return n0;")
     else:
@@ -155,7 +170,13 @@ def main():
              "// grn_cost_kernel.  Every stage state after the second is formed as",
              "//   ys = fma(hs*a_last*vm, sg, q),  q = y + hs*sum_{older k} + hs*a_last*(-lambda*ys_prev)",
              "// so only one FMA separates the logistic sg from the next stage state.",
-             "#pragma once", "#include <math_constants.h>", "", "namespace lassim {", ""]
+             "#pragma once", "#include <math_constants.h>", "", "namespace lassim {", "",
+             "// 1/x for x > 0 from the SFU seed (MUFU.RCP64H) and one Newton step: relative error <= 1e-12",
+             "__device__ __forceinline__ double fast_rcp(double x) {",
+             "    double r;",
+             "    asm(\"rcp.approx.ftz.f64 %0, %1;\" : \"=d\"(r) : \"d\"(x));",
+             "    return fma(r, fma(-x, r, 1.0), r);",
+             "}", ""]
     parts.append(emit(dp45()))
     parts.append(emit(dop853()))
     parts.append("}  // namespace lassim\n")
