@@ -269,6 +269,22 @@ def run_ours(args):
     dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
     ok = bool((dstatus == 0).all().item()) and bool(torch.isfinite(dcost).all().item())
 
+    # the other Dormand-Prince pair on the same population (outside the timed region):
+    # the headline uses --method (default 8(5,3)); BASELINE.json's north_star names 5(4)
+    other = None
+    if rank == 0 and world == 1:
+        alt = "dp45" if args.method == "dop853" else "dop853"
+        eng.set_method(alt)
+        ms_alt = []
+        for _ in range(3):
+            step_device()
+            torch.cuda.synchronize()
+            ms_alt.append(eng.last_kernel_ms())
+        other = {"integrator": {"dop853": "Dormand-Prince 8(5,3)", "dp45": "Dormand-Prince 5(4)"}[alt],
+                 "kernel_ms": float(np.median(ms_alt[1:])),
+                 "evals_per_s": POP / (float(np.median(ms_alt[1:])) * 1e-3)}
+        eng.set_method(args.method)
+
     # the same kernel with the machine kept full (16 copies of the population):
     # separates kernel quality from the single-population critical path
     sat = None
@@ -345,6 +361,8 @@ def run_ours(args):
                                                    "does when the batch outlasts its longest "
                                                    "trajectory")},
         }
+        if other is not None:
+            line["other_integrator"] = other
         if world == 1 and not args.no_cpu_baseline:
             arm = CpuArm(p)
             S = sample_size(arm.cores, 4)
