@@ -29,6 +29,8 @@ def perturbation_func_sequential(pert_data, size, y0, sol_vector, vector_map,
         key = ("pert", size, pert_data.tobytes(), y0.tobytes(), mask.tobytes())
         token = _engine._plugin_engines.get(key)
         if token is None:
+            if len(_engine._plugin_engines) > 256:     # keys hold whole arrays: keep the cache small
+                _engine._plugin_engines.clear()
             token = _engine._plugin_engines[key] = _engine.new_token()
         times = np.array([pert_data[0, size], pert_data[0, size + 1]])
         _engine.bind(eng, token, np.zeros((2, size)), np.ones(size), times, y0,
