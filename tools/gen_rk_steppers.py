@@ -164,6 +164,123 @@ def emit(tb):
     return "\n".join(L)
 
 
+def emit_incremental(tb):
+    """Same attempt, but every stage derivative is folded into the partial sums of ALL
+    later stages (and of the solution and error rows) as soon as it exists: independent
+    FMAs that can issue anywhere, instead of one dependent chain per stage."""
+    S, A, B, E = tb["S"], tb["A"], tb["B"], tb["E"]
+    name = tb["name"]
+    nE = len(E)
+    early = all(E[m][S] == 0.0 for m in range(nE))
+    L = []
+    w = L.append
+    w("// %s: one step attempt of size hs from (y, k1 = f(y)).  [incremental partial sums]" % name)
+    w("//   sig(ys, sg)  evaluates the logistic terms sg = sigmoid(W ys) for this lane's genes")
+    w("//   gmax(x)      max of a non-negative float over the lanes of the group")
+    w("// Outputs: yn (the order-%d solution), kn = f(yn); returns the group's error measure"
+      % tb["order"])
+    w("// (accept if <= 1), +inf when anything was non-finite.")
+    w("template <int R, class Sig, class GMax>")
+    w("__device__ __forceinline__ float %s_attempt(Sig &&sig, GMax &&gmax," % name)
+    w("        const double (&lam)[R], const double (&vm)[R], const double (&y)[R],")
+    w("        const double (&k1)[R], const double hs, const double rtol, const double atol,")
+    w("        double (&yn)[R], double (&kn)[R]) {")
+    rows = {}                                  # name -> (coefficients, folded-up-to index exclusive)
+    for s in range(2, S):
+        rows["a%d" % s] = A[s][:s - 1]
+    rows["ab"] = B[:S - 1]
+    for m in range(nE):
+        rows["ae%d" % m] = E[m][:S]
+    w("    double %s;" % ", ".join("%s[R]" % r for r in rows))
+    w("    double ys[R], sg[R], q[R], ly[R], cv[R], kc[R];")
+    started = set()
+
+    def fold(j, kname):
+        lines = []
+        for rname, coefs in rows.items():
+            if j < len(coefs) and coefs[j] != 0.0:
+                if rname in started:
+                    lines.append("            %s[r] = fma(%s, %s[r], %s[r]);" % (rname, lit(coefs[j]), kname, rname))
+                else:
+                    lines.append("            %s[r] = %s * %s[r];" % (rname, lit(coefs[j]), kname))
+                    started.add(rname)
+        return lines
+
+    w("#pragma unroll")
+    w("    for (int r = 0; r < R; ++r) {")
+    w("        ys[r] = fma(hs * %s, k1[r], y[r]);" % lit(A[1][0]))
+    for line in fold(0, "k1"):
+        w(line[4:])
+    w("    }")
+    for s in range(2, S + 1):
+        row = A[s] if s < S else B
+        last = row[s - 1]
+        target = "ys" if s < S else "yn"
+        acc = ("a%d" % s) if s < S else "ab"
+        w("    {   // sigma at stage %d's state -> k%d, %s" % (s, s, "state of stage %d" % (s + 1) if s < S else "yn"))
+        w("        const double hl = hs * %s;" % lit(last))
+        w("#pragma unroll")
+        w("        for (int r = 0; r < R; ++r) {")
+        w("            ly[r] = -lam[r] * ys[r];")
+        w("            cv[r] = hl * vm[r];")
+        accexpr = "%s[r]" % acc if acc in started else "0.0"
+        w("            q[r] = fma(hl, ly[r], fma(hs, %s, y[r]));" % accexpr)
+        w("        }")
+        w("        sig(ys, sg);")
+        w("#pragma unroll")
+        w("        for (int r = 0; r < R; ++r) {")
+        w("            %s[r] = fma(cv[r], sg[r], q[r]);" % target)
+        w("            kc[r] = fma(vm[r], sg[r], ly[r]);")
+        for line in fold(s - 1, "kc"):
+            w(line)
+        w("        }")
+        w("    }")
+    w("    double isc[R];")
+    w("#pragma unroll")
+    w("    for (int r = 0; r < R; ++r) {")
+    w("        ly[r] = -lam[r] * yn[r];")
+    w("        isc[r] = fast_rcp(fma(rtol, fmax(fabs(y[r]), fabs(yn[r])), atol));")
+    w("    }")
+
+    def measure(with_last):
+        for m in range(nE):
+            w("    double qd%d = 0.0;" % m)
+        w("#pragma unroll")
+        w("    for (int r = 0; r < R; ++r) {")
+        for m in range(nE):
+            acc = "ae%d[r]" % m if ("ae%d" % m) in started else "0.0"
+            if with_last and E[m][S] != 0.0:
+                w("        const double e%d = hs * fma(%s, kn[r], %s);" % (m, lit(E[m][S]), acc))
+            else:
+                w("        const double e%d = hs * %s;" % (m, acc))
+            w("        qd%d = fmax(qd%d, fabs(e%d) * isc[r]);      // fmax drops NaN: checked next" % (m, m, m))
+            w("        if (e%d != e%d) qd%d = CUDART_INF;" % (m, m, m))
+        w("    }")
+        for m in range(nE):
+            w("    const float n%d = gmax((qd%d <= 3.0e38) ? (float)qd%d : CUDART_INF_F);" % (m, m, m))
+
+    if early:
+        measure(False)
+        w("    sig(yn, sg);")
+        w("#pragma unroll")
+        w("    for (int r = 0; r < R; ++r) kn[r] = fma(vm[r], sg[r], ly[r]);")
+    else:
+        w("    sig(yn, sg);")
+        w("#pragma unroll")
+        w("    for (int r = 0; r < R; ++r) kn[r] = fma(vm[r], sg[r], ly[r]);")
+        measure(True)
+    if nE == 1:
+        w("    return n0;")
+    else:
+        w("    // Hairer's 8(5,3) measure err5^2 / sqrt(err5^2 + 0.01 err3^2), in the max-norm")
+        w("    if (!(n0 < 1.0e18f) || !(n1 < 1.0e18f)) return CUDART_INF_F;")
+        w("    const float den = fmaf(n0, n0, 0.01f * n1 * n1);")
+        w("    return den > 0.0f ? n0 * n0 * rsqrtf(den) : 0.0f;")
+    w("}")
+    w("")
+    return "\n".join(L)
+
+
 def main():
     parts = ["// GENERATED by tools/gen_rk_steppers.py - do not edit by hand.",
              "// Fully unrolled step attempts of the explicit Runge-Kutta pairs used by",
@@ -177,8 +294,9 @@ def main():
              "    asm(\"rcp.approx.ftz.f64 %0, %1;\" : \"=d\"(r) : \"d\"(x));",
              "    return fma(r, fma(-x, r, 1.0), r);",
              "}", ""]
-    parts.append(emit(dp45()))
-    parts.append(emit(dop853()))
+    gen = emit_incremental if os.environ.get("LASSIM_RK_INCREMENTAL", "0") != "0" else emit
+    parts.append(gen(dp45()))
+    parts.append(gen(dop853()))
     parts.append("}  // namespace lassim\n")
     with open(OUT, "w") as fh:
         fh.write("\n".join(parts))
