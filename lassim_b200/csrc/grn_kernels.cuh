@@ -76,6 +76,9 @@ struct DevBatch {
     unsigned int work_count;  //   of the N*K items (item w: trajectory w / N of candidate w % N)
 };
 
+#ifndef LASSIM_FACMAX
+#define LASSIM_FACMAX 10.0f
+#endif
 enum { kMethodDP45 = 0, kMethodDOP853 = 1 };
 
 // threads per CTA for a group of L lanes
@@ -428,17 +431,20 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
     const double rtol = P.rtol, atol = P.atol;
     constexpr float kExpo = (METHOD == kMethodDOP853) ? -0.125f : -0.2f;
 
-    double y[R], k1[R], yn[R], kn[R], lam[R], vm[R];
+    // integrating factor for growing genes (rk_steppers.cuh): standard kernels only
+    constexpr bool kIF = !SHADOW && !PERIPH;
+    double y[R], k1[R], yn[R], kn[R], lam[R], vm[R], gr[R];
     WT wts;
     wts.clear();                       // finite placeholders until work arrives
     bool gene_ok[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         gene_ok[r] = (lg * R + r) < n;
-        y[r] = 0.0; k1[r] = 0.0; lam[r] = 0.0; vm[r] = 0.0;
+        y[r] = 0.0; k1[r] = 0.0; lam[r] = 0.0; vm[r] = 0.0; gr[r] = 0.0;
     }
 
     bool active = false, exhausted = false;
+    bool grow = false;     // this group's trajectory has a gene with negative lambda
     int c = 0, k = 0, ti = 1, nt = 2, cur = 0, st = 0, pg = 0;
     unsigned nacc = 0, nrej = 0;
     bool rejected = false;
@@ -511,6 +517,16 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                     }
                     wts.load(P, x, lg, gene_ok, FAST ? kSigScale : 1.0);
                 }
+                // lambda = lam - gr with lam >= 0 and gr >= 0: a knocked-down gene whose
+                // lambda went negative grows like exp(gr t); the steppers treat that
+                // factor exactly (NaN stays in lam)
+                double any_growth = 0.0;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    gr[r] = 0.0;
+                    if (kIF && lam[r] < 0.0) { gr[r] = -lam[r]; lam[r] = 0.0; any_growth = 1.0; }
+                }
+                grow = kIF && G::max_group(any_growth, gmask, red) > 0.0;
                 if (k == 0) { tl = P.times; nt = P.T; }
                 else { tl = P.traj_tt + 2 * k; nt = 2; }
                 t = tl[0];
@@ -529,26 +545,27 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                 sigma(y, sg, false);
 #pragma unroll
                 for (int r = 0; r < R; ++r) k1[r] = fma(vm[r], sg[r], -lam[r] * y[r]);
+                // (k1 is the derivative without the growth term; the norms use all of it)
                 double d0 = 0.0, d1 = 0.0;
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
                     const double sc = fma(rtol, fabs(y[r]), atol);
                     d0 = fmax(d0, fabs(y[r]) / sc);
-                    d1 = fmax(d1, fabs(k1[r]) / sc);
+                    d1 = fmax(d1, fabs(fma(gr[r], y[r], k1[r])) / sc);
                 }
                 d0 = G::max_group(d0, gmask, red);
                 d1 = G::max_group(d1, gmask, red);
                 const double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
 #pragma unroll
-                for (int r = 0; r < R; ++r) ys[r] = fma(h0, k1[r], y[r]);
+                for (int r = 0; r < R; ++r) ys[r] = fma(h0, fma(gr[r], y[r], k1[r]), y[r]);
                 sigma(ys, sg, false);
 #pragma unroll
-                for (int r = 0; r < R; ++r) k2[r] = fma(vm[r], sg[r], -lam[r] * ys[r]);
+                for (int r = 0; r < R; ++r) k2[r] = fma(vm[r], sg[r], (gr[r] - lam[r]) * ys[r]);
                 double d2 = 0.0;
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
                     const double sc = fma(rtol, fabs(y[r]), atol);
-                    d2 = fmax(d2, fabs(k2[r] - k1[r]) / sc);
+                    d2 = fmax(d2, fabs(k2[r] - fma(gr[r], y[r], k1[r])) / sc);
                 }
                 d2 = G::max_group(d2, gmask, red) / h0;
                 const double dm = fmax(d1, d2);
@@ -578,11 +595,28 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
             const double hs_full = hs;
             if (SHADOW && gw == 1) hs = hs_full * kShadowRatio;
 
+            // integrating factor only where some live trajectory of the domain grows
+            bool use_if = false;
+            if constexpr (kIF) {
+                if constexpr (kWarp) use_if = __any_sync(0xffffffffu, active && grow);
+                else use_if = grow;
+            }
             float qf;
-            if constexpr (METHOD == kMethodDOP853)
-                qf = dop853_attempt<R>(sig_step, gmax_step, lam, vm, y, k1, hs, rtol, atol, yn, kn);
-            else
-                qf = dp45_attempt<R>(sig_step, gmax_step, lam, vm, y, k1, hs, rtol, atol, yn, kn);
+            if constexpr (METHOD == kMethodDOP853) {
+                if (use_if)
+                    qf = dop853_attempt<kIF, R>(sig_step, gmax_step, lam, vm, gr, tab, y, k1, hs,
+                                                rtol, atol, yn, kn);
+                else
+                    qf = dop853_attempt<false, R>(sig_step, gmax_step, lam, vm, gr, tab, y, k1, hs,
+                                                  rtol, atol, yn, kn);
+            } else {
+                if (use_if)
+                    qf = dp45_attempt<kIF, R>(sig_step, gmax_step, lam, vm, gr, tab, y, k1, hs,
+                                              rtol, atol, yn, kn);
+                else
+                    qf = dp45_attempt<false, R>(sig_step, gmax_step, lam, vm, gr, tab, y, k1, hs,
+                                                rtol, atol, yn, kn);
+            }
 
             bool fallback = false;     // the shorter attempt is the one that counts
             if constexpr (SHADOW) {
@@ -613,7 +647,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                     t = hit ? tend : t + hs;
 #pragma unroll
                     for (int r = 0; r < R; ++r) { y[r] = yn[r]; k1[r] = kn[r]; }
-                    float fac = fminf(10.0f, fmaxf(0.2f, fac0));
+                    float fac = fminf(LASSIM_FACMAX, fmaxf(0.2f, fac0));
                     if (rejected) fac = fminf(fac, 1.0f);
                     rejected = fallback;     // the proposed step did fail: no growth next time
                     const double hnew = hs * (double)fac;
@@ -705,7 +739,8 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
             // park: until new work arrives this group only goes through the
             // motions of the step loop with its warp; keep its registers finite
 #pragma unroll
-            for (int r = 0; r < R; ++r) { y[r] = 0.0; k1[r] = 0.0; }
+            for (int r = 0; r < R; ++r) { y[r] = 0.0; k1[r] = 0.0; gr[r] = 0.0; }
+            grow = false;
             h = 0.0; t = 0.0; tend = 0.0;
             if (B.mode == 0) {
                 __threadfence();

@@ -11,6 +11,9 @@ import numpy as np
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, REPO)
 sys.path.insert(0, os.path.join(REPO, "tools"))
+from lassim_b200 import _capi  # noqa: E402
+if os.environ.get('LASSIM_LIB'):
+    _capi._LIB_PATH = os.path.join(REPO, 'lassim_b200', os.environ['LASSIM_LIB'])
 from lassim_b200 import Engine  # noqa: E402
 from workloads import stiff_population, synthetic_problem, uniform_population  # noqa: E402
 

@@ -36,7 +36,8 @@ def dp45():
     B = [F(35, 384), 0, F(500, 1113), F(125, 192), F(-2187, 6784), F(11, 84)]
     E = [F(71, 57600), 0, F(-71, 16695), F(71, 1920), F(-17253, 339200), F(22, 525), F(-1, 40)]
     A = [[float(x) for x in row] for row in A]
-    return dict(name="dp45", S=6, order=5, A=A, B=[float(b) for b in B],
+    C = [0.0, 1 / 5, 3 / 10, 4 / 5, 8 / 9, 1.0, 1.0]
+    return dict(name="dp45", S=6, order=5, A=A, B=[float(b) for b in B], C=C,
                 E=[[float(e) for e in E]])
 
 
@@ -45,6 +46,7 @@ def dop853():
     S = 12
     A = [[float(dc.A[s, j]) for j in range(s)] for s in range(S)]
     return dict(name="dop853", S=S, order=8, A=A, B=[float(b) for b in dc.B],
+                C=[float(c) for c in dc.C[:S]] + [1.0],
                 E=[[float(e) for e in dc.E5], [float(e) for e in dc.E3]])
 
 
@@ -60,65 +62,89 @@ def weighted_sum(coefs, names, indent):
 
 
 def emit(tb):
-    S, A, B, E = tb["S"], tb["A"], tb["B"], tb["E"]
+    S, A, B, C, E = tb["S"], tb["A"], tb["B"], tb["C"], tb["E"]
     name = tb["name"]
     K = ["k%d" % (i + 1) for i in range(S + 1)]          # k1 .. k_{S+1}
     L = []
     w = L.append
-    w("// %s: one step attempt of size hs from (y, k1 = f(y))." % name)
+    w("// %s: one step attempt of size hs from (y, k1)." % name)
     w("//   sig(ys, sg)  evaluates the logistic terms sg = sigmoid(W ys) for this lane's genes")
     w("//   gmax(x)      max of a non-negative float over the lanes of the group")
-    w("// Outputs: yn (the order-%d solution), kn = f(yn); returns the group's error measure"
+    w("// Outputs: yn (the order-%d solution), kn (first stage derivative of the next step);"
       % tb["order"])
-    w("// (accept if <= 1), +inf when anything was non-finite.")
-    w("template <int R, class Sig, class GMax>")
+    w("// returns the group's error measure (accept if <= 1), +inf when anything was non-finite.")
+    w("//")
+    w("// IF = true: integrating factor for exponentially GROWING genes.  With lambda = lp - gr")
+    w("// (lp >= 0, gr >= 0 the growth rate of a knocked-down gene whose lambda went negative),")
+    w("// the pair is applied to u(tau) = exp(-gr tau) y(t_n + tau), for which")
+    w("//     u' = exp(-gr tau) G(exp(gr tau) u),   G(y) = -lp*y + vmax*sigmoid(W y),")
+    w("// so the homogeneous growth is exact and the step size is set by the rest of the")
+    w("// dynamics.  `lam` then holds lp, `k1`/`kn` are G(y)/G(yn), stage derivatives live in")
+    w("// u-space (K_s = -lp*U_s + vmax*exp(-gr c_s h)*sg), errors are mapped back to y.  Genes")
+    w("// with gr = 0 see exactly the plain formulas.")
+    w("template <bool IF, int R, class Sig, class GMax>")
     w("__device__ __forceinline__ float %s_attempt(Sig &&sig, GMax &&gmax," % name)
-    w("        const double (&lam)[R], const double (&vm)[R], const double (&y)[R],")
+    w("        const double (&lam)[R], const double (&vm)[R], const double (&gr)[R],")
+    w("        const double *tab, const double (&y)[R],")
     w("        const double (&k1)[R], const double hs, const double rtol, const double atol,")
     w("        double (&yn)[R], double (&kn)[R]) {")
     decl = ", ".join("%s[R]" % k for k in K[1:S])
     w("    double %s;" % decl)
-    w("    double ys[R], sg[R], q[R], ly[R], cv[R];")
+    w("    double ys[R], sg[R], q[R], ly[R], cv[R], ef[R], ei[R], yz[R];")
     w("#pragma unroll")
-    w("    for (int r = 0; r < R; ++r) ys[r] = fma(hs * %s, k1[r], y[r]);" % lit(A[1][0]))
+    w("    for (int r = 0; r < R; ++r) { ys[r] = fma(hs * %s, k1[r], y[r]); ef[r] = 1.0; ei[r] = 1.0; }" % lit(A[1][0]))
     for s in range(2, S + 1):
         row = A[s] if s < S else B
         last = row[s - 1]
+        c = C[s - 1]
         target = "ys" if s < S else "yn"
-        w("    {   // sigma at stage %d's state -> %s, %s" % (s, K[s - 1], "state of stage %d" % (s + 1) if s < S else "yn"))
+        w("    {   // sigma at stage %d's state (c = %s) -> %s, %s" % (s, lit(c), K[s - 1], "state of stage %d" % (s + 1) if s < S else "solution"))
         w("        const double hl = hs * %s;" % lit(last))
+        w("        if constexpr (IF) {")
+        w("#pragma unroll")
+        w("            for (int r = 0; r < R; ++r) {")
+        w("                ef[r] = exp2_tab(gr[r] * (hs * %s), tab);" % lit(c * 1.4426950408889634))
+        w("                ei[r] = (gr[r] == 0.0) ? 1.0 : fast_rcp(ef[r]);")
+        w("                yz[r] = ef[r] * ys[r];")
+        w("            }")
+        w("        }")
         w("#pragma unroll")
         w("        for (int r = 0; r < R; ++r) {")
         w("            ly[r] = -lam[r] * ys[r];")
-        w("            cv[r] = hl * vm[r];")
+        w("            cv[r] = IF ? (hl * vm[r]) * ei[r] : hl * vm[r];")
         w("            q[r] = fma(hl, ly[r], fma(hs, %s, y[r]));" % weighted_sum(row[:s - 1], K[:s - 1], 16))
         w("        }")
-        w("        sig(ys, sg);")
+        w("        if constexpr (IF) sig(yz, sg); else sig(ys, sg);")
         w("#pragma unroll")
         w("        for (int r = 0; r < R; ++r) {")
         w("            %s[r] = fma(cv[r], sg[r], q[r]);" % target)
-        w("            %s[r] = fma(vm[r], sg[r], ly[r]);" % K[s - 1])
+        w("            %s[r] = fma(IF ? vm[r] * ei[r] : vm[r], sg[r], ly[r]);" % K[s - 1])
         w("        }")
         w("    }")
+    assert abs(C[S - 1] - 1.0) < 1e-15, "the last stage sits at c = 1: ef is exp(gr*hs) there"
     # last evaluation f(yn) and the error estimates
     nE = len(E)
     early = all(E[m][S] == 0.0 for m in range(nE))     # the estimate does not need f(yn)
-    w("    // f(yn) (first stage of the next step) and the error estimate%s" % ("s" if nE > 1 else ""))
+    w("    // back to y (ef = exp(gr*hs) from the last stage, at c = 1), then f(yn) (first stage of")
+    w("    // the next step) and the error estimate%s" % ("s" if nE > 1 else ""))
     w("    double isc[R];")
     for m in range(nE):
         w("    double eq%d[R], ce%d[R];" % (m, m))
     w("#pragma unroll")
     w("    for (int r = 0; r < R; ++r) {")
+    w("        if constexpr (IF) yn[r] *= ef[r];")
     w("        ly[r] = -lam[r] * yn[r];")
     for m in range(nE):
         e_last = E[m][S]
         base = "hs * (%s)" % weighted_sum(E[m][:S], K[:S], 8)
+        w("        { const double base = %s;" % base)
+        w("          const double eb = IF ? ef[r] * base : base;      // u-space sum mapped to y")
         if e_last != 0.0:
-            w("        ce%d[r] = (hs * %s) * vm[r];" % (m, lit(e_last)))
-            w("        eq%d[r] = fma(hs * %s, ly[r], %s);" % (m, lit(e_last), base))
+            w("          ce%d[r] = (hs * %s) * vm[r];" % (m, lit(e_last)))
+            w("          eq%d[r] = fma(hs * %s, ly[r], eb); }" % (m, lit(e_last)))
         else:
-            w("        ce%d[r] = 0.0;" % m)
-            w("        eq%d[r] = %s;" % (m, base))
+            w("          ce%d[r] = 0.0;" % m)
+            w("          eq%d[r] = eb; }" % m)
     w("        // error weight rtol*max(|y|,|yn|) + atol; its reciprocal to 1e-12 is plenty for a")
     w("        // step-size decision and keeps an IEEE division off the path")
     w("        isc[r] = fast_rcp(fma(rtol, fmax(fabs(y[r]), fabs(yn[r])), atol));")
@@ -164,123 +190,6 @@ def emit(tb):
     return "\n".join(L)
 
 
-def emit_incremental(tb):
-    """Same attempt, but every stage derivative is folded into the partial sums of ALL
-    later stages (and of the solution and error rows) as soon as it exists: independent
-    FMAs that can issue anywhere, instead of one dependent chain per stage."""
-    S, A, B, E = tb["S"], tb["A"], tb["B"], tb["E"]
-    name = tb["name"]
-    nE = len(E)
-    early = all(E[m][S] == 0.0 for m in range(nE))
-    L = []
-    w = L.append
-    w("// %s: one step attempt of size hs from (y, k1 = f(y)).  [incremental partial sums]" % name)
-    w("//   sig(ys, sg)  evaluates the logistic terms sg = sigmoid(W ys) for this lane's genes")
-    w("//   gmax(x)      max of a non-negative float over the lanes of the group")
-    w("// Outputs: yn (the order-%d solution), kn = f(yn); returns the group's error measure"
-      % tb["order"])
-    w("// (accept if <= 1), +inf when anything was non-finite.")
-    w("template <int R, class Sig, class GMax>")
-    w("__device__ __forceinline__ float %s_attempt(Sig &&sig, GMax &&gmax," % name)
-    w("        const double (&lam)[R], const double (&vm)[R], const double (&y)[R],")
-    w("        const double (&k1)[R], const double hs, const double rtol, const double atol,")
-    w("        double (&yn)[R], double (&kn)[R]) {")
-    rows = {}                                  # name -> (coefficients, folded-up-to index exclusive)
-    for s in range(2, S):
-        rows["a%d" % s] = A[s][:s - 1]
-    rows["ab"] = B[:S - 1]
-    for m in range(nE):
-        rows["ae%d" % m] = E[m][:S]
-    w("    double %s;" % ", ".join("%s[R]" % r for r in rows))
-    w("    double ys[R], sg[R], q[R], ly[R], cv[R], kc[R];")
-    started = set()
-
-    def fold(j, kname):
-        lines = []
-        for rname, coefs in rows.items():
-            if j < len(coefs) and coefs[j] != 0.0:
-                if rname in started:
-                    lines.append("            %s[r] = fma(%s, %s[r], %s[r]);" % (rname, lit(coefs[j]), kname, rname))
-                else:
-                    lines.append("            %s[r] = %s * %s[r];" % (rname, lit(coefs[j]), kname))
-                    started.add(rname)
-        return lines
-
-    w("#pragma unroll")
-    w("    for (int r = 0; r < R; ++r) {")
-    w("        ys[r] = fma(hs * %s, k1[r], y[r]);" % lit(A[1][0]))
-    for line in fold(0, "k1"):
-        w(line[4:])
-    w("    }")
-    for s in range(2, S + 1):
-        row = A[s] if s < S else B
-        last = row[s - 1]
-        target = "ys" if s < S else "yn"
-        acc = ("a%d" % s) if s < S else "ab"
-        w("    {   // sigma at stage %d's state -> k%d, %s" % (s, s, "state of stage %d" % (s + 1) if s < S else "yn"))
-        w("        const double hl = hs * %s;" % lit(last))
-        w("#pragma unroll")
-        w("        for (int r = 0; r < R; ++r) {")
-        w("            ly[r] = -lam[r] * ys[r];")
-        w("            cv[r] = hl * vm[r];")
-        accexpr = "%s[r]" % acc if acc in started else "0.0"
-        w("            q[r] = fma(hl, ly[r], fma(hs, %s, y[r]));" % accexpr)
-        w("        }")
-        w("        sig(ys, sg);")
-        w("#pragma unroll")
-        w("        for (int r = 0; r < R; ++r) {")
-        w("            %s[r] = fma(cv[r], sg[r], q[r]);" % target)
-        w("            kc[r] = fma(vm[r], sg[r], ly[r]);")
-        for line in fold(s - 1, "kc"):
-            w(line)
-        w("        }")
-        w("    }")
-    w("    double isc[R];")
-    w("#pragma unroll")
-    w("    for (int r = 0; r < R; ++r) {")
-    w("        ly[r] = -lam[r] * yn[r];")
-    w("        isc[r] = fast_rcp(fma(rtol, fmax(fabs(y[r]), fabs(yn[r])), atol));")
-    w("    }")
-
-    def measure(with_last):
-        for m in range(nE):
-            w("    double qd%d = 0.0;" % m)
-        w("#pragma unroll")
-        w("    for (int r = 0; r < R; ++r) {")
-        for m in range(nE):
-            acc = "ae%d[r]" % m if ("ae%d" % m) in started else "0.0"
-            if with_last and E[m][S] != 0.0:
-                w("        const double e%d = hs * fma(%s, kn[r], %s);" % (m, lit(E[m][S]), acc))
-            else:
-                w("        const double e%d = hs * %s;" % (m, acc))
-            w("        qd%d = fmax(qd%d, fabs(e%d) * isc[r]);      // fmax drops NaN: checked next" % (m, m, m))
-            w("        if (e%d != e%d) qd%d = CUDART_INF;" % (m, m, m))
-        w("    }")
-        for m in range(nE):
-            w("    const float n%d = gmax((qd%d <= 3.0e38) ? (float)qd%d : CUDART_INF_F);" % (m, m, m))
-
-    if early:
-        measure(False)
-        w("    sig(yn, sg);")
-        w("#pragma unroll")
-        w("    for (int r = 0; r < R; ++r) kn[r] = fma(vm[r], sg[r], ly[r]);")
-    else:
-        w("    sig(yn, sg);")
-        w("#pragma unroll")
-        w("    for (int r = 0; r < R; ++r) kn[r] = fma(vm[r], sg[r], ly[r]);")
-        measure(True)
-    if nE == 1:
-        w("    return n0;")
-    else:
-        w("    // Hairer's 8(5,3) measure err5^2 / sqrt(err5^2 + 0.01 err3^2), in the max-norm")
-        w("    if (!(n0 < 1.0e18f) || !(n1 < 1.0e18f)) return CUDART_INF_F;")
-        w("    const float den = fmaf(n0, n0, 0.01f * n1 * n1);")
-        w("    return den > 0.0f ? n0 * n0 * rsqrtf(den) : 0.0f;")
-    w("}")
-    w("")
-    return "\n".join(L)
-
-
 def main():
     parts = ["// GENERATED by tools/gen_rk_steppers.py - do not edit by hand.",
              "// Fully unrolled step attempts of the explicit Runge-Kutta pairs used by",
@@ -293,10 +202,23 @@ def main():
              "    double r;",
              "    asm(\"rcp.approx.ftz.f64 %0, %1;\" : \"=d\"(r) : \"d\"(x));",
              "    return fma(r, fma(-x, r, 1.0), r);",
+             "}", "",
+             "// 2^a for a >= 0 (clamped at 1000) with the kernel's 2^(j/256) table in shared memory:",
+             "// a = n + j/256 + f, |f| <= 2^-9, degree-3 Taylor of (2^f - 1)/f; exactly 1 for a = 0.",
+             "__device__ __forceinline__ double exp2_tab(double a, const double *tab) {",
+             "    a = fmin(a, 1000.0);",
+             "    const double kMagic = 26388279066624.0;    // 1.5 * 2^44: ulp = 1/256",
+             "    const double s = a + kMagic;",
+             "    const int ki = __double2loint(s);",
+             "    const double f = a - (s - kMagic);",
+             "    const double tj = tab[ki & 255];",
+             "    const double p = fma(f * f, fma(0.009618129107628477, f, 0.05550410866482158),",
+             "                         fma(0.2402265069591007, f, 0.6931471805599453));",
+             "    const double v = fma(tj, f * p, tj);",
+             "    return __hiloint2double(__double2hiint(v) + ((ki >> 8) << 20), __double2loint(v));",
              "}", ""]
-    gen = emit_incremental if os.environ.get("LASSIM_RK_INCREMENTAL", "0") != "0" else emit
-    parts.append(gen(dp45()))
-    parts.append(gen(dop853()))
+    parts.append(emit(dp45()))
+    parts.append(emit(dop853()))
     parts.append("}  // namespace lassim\n")
     with open(OUT, "w") as fh:
         fh.write("\n".join(parts))
