@@ -90,17 +90,24 @@ int lassim_set_tolerances(lassim_handle *h, double rtol, double atol,
 enum { LASSIM_METHOD_DP45 = 0, LASSIM_METHOD_DOP853 = 1 };
 int lassim_set_method(lassim_handle *h, int method);
 
-/* Speculative step attempts for the time-series trajectories (problems of at
- * most 16 genes): every attempt is made at the proposed step size and, by the
- * other half of the warp, at 0.7 of it; when the full step fails its error test
- * and the shorter one passes, the shorter one is accepted instead of starting
- * over.  Removes about a fifth of the sequential attempts on trajectories with
- * many rejections, which is what a small batch waits for; uses twice the lanes
- * for those trajectories.  0 = off, 1 = on, 2 = automatic (default: on for
- * batches of at most 2048 candidates).  Results are deterministic for a given
- * setting and batch-size class, and stay inside the same error control.  (No
- * reference counterpart.)  LASSIM_SPECULATE in the environment sets the initial
- * mode. */
+/* Kernel for the time-series trajectories of problems of at most 16 genes.  A
+ * small batch waits for its longest time series, so these modes trade lanes for
+ * fewer SEQUENTIAL right-hand sides on that trajectory (one warp per trajectory):
+ *   0  the standard kernel (16 lanes per trajectory, the pair lassim_set_method names)
+ *   1  speculative attempts: every attempt is made at the proposed step size and,
+ *      by the other half of the warp, at 0.7 of it; when the full step fails its
+ *      error test and the shorter one passes, the shorter one is accepted
+ *      instead of starting over (a fifth fewer sequential attempts on limit cycles)
+ *   3  stage-parallel: a 5-stage Gauss collocation pair (4-stage above 12 genes)
+ *      solved by fixed-point iteration with its stages side by side in the warp,
+ *      6 (5) sequential right-hand sides per attempt instead of 12, same
+ *      tolerances, weights and norm; steps are also limited so that no logistic
+ *      term swings by more than 0.5 inside one (csrc/pirk_kernel.cuh)
+ *   2  automatic (default): 3 for batches of at most 2048 candidates, else 0
+ * Results are deterministic for a given mode and batch-size class and stay inside
+ * the same error control; the knock-down trajectories always run on the standard
+ * kernel.  (No reference counterpart.)  LASSIM_SPECULATE in the environment sets
+ * the initial mode. */
 int lassim_set_speculation(lassim_handle *h, int mode);
 
 /* Current decision-vector length (2n + nnz), trajectories per candidate

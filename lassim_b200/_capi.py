@@ -191,11 +191,14 @@ class Engine:
                     "lassim_set_tolerances")
 
     def set_speculation(self, mode="auto"):
-        """Speculative half-warp step attempts for time-series trajectories:
-        'off', 'on' or 'auto' (on for batches of at most 2048 candidates)."""
-        code = {"off": 0, "on": 1, "auto": 2, 0: 0, 1: 1, 2: 2, False: 0, True: 1}.get(mode)
+        """Kernel for the time-series trajectories: 'off' (the standard one), 'on'
+        (speculative half-warp attempts), 'stages' (stage-parallel Gauss pair, one warp
+        per trajectory) or 'auto' ('stages' for batches of at most 2048 candidates)."""
+        code = {"off": 0, "on": 1, "auto": 2, "stages": 3, 0: 0, 1: 1, 2: 2, 3: 3,
+                False: 0, True: 1}.get(mode)
         if code is None:
-            raise ValueError("speculation mode %r (use 'off', 'on' or 'auto')" % (mode,))
+            raise ValueError("time-series kernel mode %r (use 'off', 'on', 'stages' or 'auto')"
+                             % (mode,))
         self._check(self._lib.lassim_set_speculation(self._h, code), "lassim_set_speculation")
 
     def set_method(self, method="dop853"):

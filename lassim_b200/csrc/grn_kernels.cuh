@@ -91,10 +91,12 @@ constexpr int threads_for(int L) { return L > 32 ? L : (L == 4 ? 256 : 128); }
 #endif
 constexpr int min_blocks_for(int L) { return (L == 16 || L == 32) ? LASSIM_MIN_BLOCKS : 1; }
 
-// doubles of shared memory in front of the groups' exchange lines:
-// 256 (2^(j/256) table) + 32 (reduction / broadcast scratch of a CTA-wide group)
+// doubles of shared memory in front of the groups' exchange lines: the 2^(j/256) table
+// (256 entries + the two saturation entries 0 and 2^1000, padded to 264) + 32 of
+// reduction / broadcast scratch for a CTA-wide group
 constexpr int kExpTable = 256;
-constexpr int kSmemHeader = kExpTable + 32;
+constexpr int kTabDoubles = 264;
+constexpr int kSmemHeader = kTabDoubles + 32;
 
 // 2^(j/256), j = 0..255, filled by the host when the engine is created.
 __constant__ double c_exp2_table[kExpTable];
@@ -110,40 +112,54 @@ __device__ __forceinline__ double logistic_libm(double z) {
     return 1.0 / (1.0 + exp(-z));
 }
 
-// 1 / (1 + 2^t), t = -z*log2(e).  With t = n + j/256 + f, |f| <= 2^-9:
-//   2^t = S * (1 + f*p(f)),  S = 2^n * T[j],  p = degree-3 Taylor of (2^f - 1)/f
-// (truncation 4e-17), so the denominator is d = fma(S, f*p, 1 + S): the table
-// value, its exponent scaling and 1 + S depend only on the rounding of t and sit
-// beside the dependent chain  t -> f -> p -> f*p -> d -> 1/d, not on it.  The
-// reciprocal is an SFU seed (MUFU.RCP64H) refined by one FP64 Newton step
-// (relative error <= 1e-12).  |t| >= 1000 (also NaN/inf) selects d = 2^1000 or 1 directly: below
-// -1000, 2^t vanishes next to 1; above, the result is < 1e-301 where the
-// reference returns vmax*exp(z) or 0 after overflow.  The test runs on the high
-// word with integer ops, in parallel with the chain.
-__device__ __forceinline__ double logistic_fast(double t, const double *tab) {
+// 1 / (1 + 2^t), t = -z*log2(e).  With t = k + j/256 + f, |f| <= 2^-9:
+//   2^t = T[j] * g,  g = 2^k * (1 + f*p(f)),  p = degree-3 Taylor of (2^f - 1)/f
+// (truncation 4e-17), so the denominator is d = fma(T[j], g, 1).  The table value
+// comes out of shared memory last, so everything else - the polynomial, the
+// exponent scaling (on g, not on T[j]) - is arranged to be ready when it arrives:
+// one FMA separates the table load from d.  |t| >= 1000 (also NaN/inf) does not
+// go through a select after d either: it redirects the LOAD to one of two extra
+// table entries, T[256] = 0 (d = 1: 2^t vanishes next to 1) and T[257] = 2^1000
+// (result < 1e-301, where the reference returns vmax*exp(z) or 0 after overflow),
+// with g = 1; the test runs on the high word with integer ops beside the chain.
+// The reciprocal is an SFU seed r (MUFU.RCP64H, relative error <= 2^-20) and ONE
+// Newton step: sigma = r + r*e, e = 1 - d*r (<= 2^-40, 1e-12 relative, four orders
+// below the integration tolerance).  r and e are returned separately: the caller
+// folds the Newton step into its own next FMA, c*sigma + q = fma(c*r, e, fma(c, r, q)),
+// two dependent operations after r instead of three.
+__device__ __forceinline__ void logistic_fast_parts(double t, const double *tab, double &r,
+                                                    double &e) {
     const int thi = __double2hiint(t);
     const bool big = (thi & 0x7fffffff) >= 0x408f4000;
     const double kMagic = 26388279066624.0;    // 1.5 * 2^44: ulp = 1/256
     const double s = t + kMagic;
     const int ki = __double2loint(s);
     const double f = t - (s - kMagic);
-    // beside the chain: S = 2^(ki >> 8) * T[ki & 255] and 1 + S
-    const double tj = tab[ki & (kExpTable - 1)];
-    const double S = __hiloint2double(__double2hiint(tj) + ((ki >> 8) << 20), __double2loint(tj));
-    const double S1 = 1.0 + S;
-    // on the chain
+    const int idx = big ? (thi < 0 ? kExpTable : kExpTable + 1) : (ki & (kExpTable - 1));
+    const double tj = tab[idx];
     const double f2 = f * f;
     const double p01 = fma(0.2402265069591007, f, 0.6931471805599453);
     const double p23 = fma(0.009618129107628477, f, 0.05550410866482158);
-    const double p = fma(f2, p23, p01);
-    double d = fma(S, f * p, S1);
-    if (big) d = (thi < 0) ? 1.0 : 1.0715086071862673e301;   // 2^1000
-    double r;
+    double g = fma(f, fma(f2, p23, p01), 1.0);
+    g = __hiloint2double(__double2hiint(g) + ((ki >> 8) << 20), __double2loint(g));
+    if (big) g = 1.0;
+    const double d = fma(tj, g, 1.0);
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
-    // one Newton step: seed error <= 2^-20 -> <= 2^-40 (1e-12 relative), four
-    // orders below the integration tolerance; a second step would add two
-    // dependent FMAs to every RHS evaluation for digits the error control never sees
-    return fma(r, fma(-d, r, 1.0), r);
+    e = fma(-d, r, 1.0);
+}
+
+__device__ __forceinline__ double logistic_fast(double t, const double *tab) {
+    double r, e;
+    logistic_fast_parts(t, tab, r, e);
+    return fma(r, e, r);
+}
+
+// fills the table part of the shared-memory header (all threads of the CTA call it)
+__device__ __forceinline__ void fill_exp2_table(double *tab) {
+    for (int i = threadIdx.x; i < kTabDoubles; i += blockDim.x)
+        tab[i] = (i < kExpTable) ? c_exp2_table[i]
+               : (i == kExpTable + 1) ? 1.0715086071862673e301   // 2^1000
+                                      : 0.0;
 }
 
 // ---------------------------------------------------------------- weights
@@ -419,9 +435,9 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
     const bool leader = SHADOW ? (lane == 0) : (lg == 0);
     const bool writer = !SHADOW || gw == 0;
     double *tab = smem;
-    double *red = smem + kExpTable;
+    double *red = smem + kTabDoubles;
     double *ybuf = smem + kSmemHeader + gid * (2 * STRIDE);
-    for (int i = threadIdx.x; i < kExpTable; i += blockDim.x) tab[i] = c_exp2_table[i];
+    fill_exp2_table(tab);
     for (int i = lg; i < 2 * STRIDE; i += L) ybuf[i] = 0.0;
     __syncthreads();
 
@@ -451,8 +467,8 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
     double t = 0.0, h = 0.0, tend = 0.0;
     const double *tl = P.times;
 
-    // sg = sigmoid(W in): publish this lane's entries, barrier, mat-vec, logistic
-    auto sigma = [&](const double (&in)[R], double (&out)[R], bool whole_domain) {
+    // sigmoid(W in) = sr + sr*se: publish this lane's entries, barrier, mat-vec, logistic
+    auto sigma = [&](const double (&in)[R], double (&sr)[R], double (&se)[R], bool whole_domain) {
         double *buf = ybuf + cur * STRIDE;
 #pragma unroll
         for (int r = 0; r < R; ++r) buf[lg * R + r] = in[r];
@@ -460,10 +476,15 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
         double z[R];
         wts.matvec(buf, z);
 #pragma unroll
-        for (int r = 0; r < R; ++r) out[r] = FAST ? logistic_fast(z[r], tab) : logistic_libm(z[r]);
+        for (int r = 0; r < R; ++r) {
+            if constexpr (FAST) logistic_fast_parts(z[r], tab, sr[r], se[r]);
+            else { sr[r] = logistic_libm(z[r]); se[r] = 0.0; }
+        }
         cur ^= 1;
     };
-    auto sig_step = [&](const double (&in)[R], double (&out)[R]) { sigma(in, out, true); };
+    auto sig_step = [&](const double (&in)[R], double (&sr)[R], double (&se)[R]) {
+        sigma(in, sr, se, true);
+    };
     auto gmax_step = [&](float v) { return G::max_domain(v, red); };
 
     while (true) {
@@ -541,10 +562,13 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                 }
                 // first derivative + starting step (Hairer/Norsett/Wanner II.4,
                 // max-norm variant)
-                double sg[R], ys[R], k2[R];
-                sigma(y, sg, false);
+                double sg[R], se[R], ys[R], k2[R];
+                sigma(y, sg, se, false);
 #pragma unroll
-                for (int r = 0; r < R; ++r) k1[r] = fma(vm[r], sg[r], -lam[r] * y[r]);
+                for (int r = 0; r < R; ++r) {
+                    sg[r] = fma(sg[r], se[r], sg[r]);
+                    k1[r] = fma(vm[r], sg[r], -lam[r] * y[r]);
+                }
                 // (k1 is the derivative without the growth term; the norms use all of it)
                 double d0 = 0.0, d1 = 0.0;
 #pragma unroll
@@ -558,9 +582,10 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                 const double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
 #pragma unroll
                 for (int r = 0; r < R; ++r) ys[r] = fma(h0, fma(gr[r], y[r], k1[r]), y[r]);
-                sigma(ys, sg, false);
+                sigma(ys, sg, se, false);
 #pragma unroll
-                for (int r = 0; r < R; ++r) k2[r] = fma(vm[r], sg[r], (gr[r] - lam[r]) * ys[r]);
+                for (int r = 0; r < R; ++r)
+                    k2[r] = fma(vm[r], fma(sg[r], se[r], sg[r]), (gr[r] - lam[r]) * ys[r]);
                 double d2 = 0.0;
 #pragma unroll
                 for (int r = 0; r < R; ++r) {

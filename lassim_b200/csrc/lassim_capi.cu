@@ -4,6 +4,7 @@
 // every evaluation entry point launches a CUDA kernel or fails.
 #include "../../include/lassim_b200.h"
 #include "grn_kernels.cuh"
+#include "pirk_kernel.cuh"
 #include "de_kernels.cuh"
 
 #include <cmath>
@@ -167,6 +168,8 @@ struct KernelChoice {
     int L, R;          // lanes per group, genes per lane
     const char *name;
     kernel_fn fn_shadow = nullptr;   // warp-per-trajectory speculative variant, if built
+    kernel_fn fn_pirk = nullptr;     // warp-per-trajectory stage-parallel variant, if built
+    size_t pirk_smem = 0;
 };
 
 // dynamic shared memory of one CTA: header (2^(j/256) table, reduction scratch)
@@ -188,6 +191,17 @@ kernel_fn shadow_kernel(int method) {
     if (method == kMethodDOP853)
         return grn_cost_kernel<16, 1, DenseW<1, NC>, kMethodDOP853, true, false, true>;
     return grn_cost_kernel<16, 1, DenseW<1, NC>, kMethodDP45, true, false, true>;
+}
+
+// stage-parallel time-series kernel: 5 Gauss stages x 6 lanes for n <= 12, 4 x 8 up to 16
+void pirk_kernel(int n, KernelChoice *out) {
+    if (n <= 12) {
+        out->fn_pirk = grn_series_pirk_kernel<5, 6, 12, true>;
+        out->pirk_smem = pirk_smem_doubles(6, 12) * sizeof(double);
+    } else {
+        out->fn_pirk = grn_series_pirk_kernel<4, 8, 16, true>;
+        out->pirk_smem = pirk_smem_doubles(8, 16) * sizeof(double);
+    }
 }
 
 template <int L>
@@ -226,11 +240,13 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
                      : nc <= 12 ? dense_kernel<16, 12>(method, fast)
                                 : dense_kernel<16, 16>(method, fast);
         *out = {fn, 16, 1, "dense 16x1"};
-        if (fast)
+        if (fast) {
             out->fn_shadow = nc <= 4 ? shadow_kernel<4>(method)
                            : nc <= 8 ? shadow_kernel<8>(method)
                            : nc <= 12 ? shadow_kernel<12>(method)
                                       : shadow_kernel<16>(method);
+            pirk_kernel(n, out);
+        }
         return true;
     }
     if (n <= 32) {
@@ -256,13 +272,19 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
 int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P,
                    const DevBatch &B, int N, int traj_per_candidate, bool periph,
                    cudaStream_t s, unsigned int *counters) {
-    const bool speculate = kc.fn_shadow != nullptr && !periph &&
-                           (h->speculate == 1 || (h->speculate == 2 && N <= 2048));
-    const size_t smem = smem_bytes(kc);
-    auto launch = [&](kernel_fn fn, int lanes_per_item, unsigned begin, unsigned count,
-                      unsigned int *counter, cudaStream_t st) -> cudaError_t {
+    // time-series kernel of a small batch: 3 = stage-parallel, 1 = speculative, 2 = auto
+    // (stage-parallel where built, for batches of at most 2048 candidates)
+    kernel_fn series_fn = nullptr;
+    if (!periph && kc.fn_pirk != nullptr &&
+        (h->speculate == 3 || (h->speculate == 2 && N <= 2048)))
+        series_fn = kc.fn_pirk;
+    else if (!periph && kc.fn_shadow != nullptr && h->speculate == 1)
+        series_fn = kc.fn_shadow;
+    const bool speculate = series_fn != nullptr;
+    const bool pirk = speculate && series_fn == kc.fn_pirk;
+    auto launch = [&](kernel_fn fn, int threads, size_t smem, int lanes_per_item, unsigned begin,
+                      unsigned count, unsigned int *counter, cudaStream_t st) -> cudaError_t {
         if (count == 0) return cudaSuccess;
-        const int threads = threads_for(kc.L);
         const int items_per_cta = threads / lanes_per_item;
         cudaError_t e = cudaFuncSetAttribute((const void *)fn,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -281,6 +303,8 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
         h->launches += 1;
         return cudaGetLastError();
     };
+    const int threads = threads_for(kc.L);
+    const size_t smem = smem_bytes(kc);
     const unsigned total = (unsigned)N * (unsigned)traj_per_candidate;
     if (speculate) {
         const unsigned rest = total - (unsigned)N;
@@ -288,14 +312,15 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
             CU(cudaEventRecord(h->ev_fork, s));
             CU(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
         }
-        CU(launch(kc.fn_shadow, 32, 0u, (unsigned)N, counters, s));
+        if (pirk) CU(launch(series_fn, kPirkThreads, kc.pirk_smem, 32, 0u, (unsigned)N, counters, s));
+        else CU(launch(series_fn, threads, smem, 32, 0u, (unsigned)N, counters, s));
         if (rest > 0) {
-            CU(launch(kc.fn, kc.L, (unsigned)N, rest, counters + 1, h->stream2));
+            CU(launch(kc.fn, threads, smem, kc.L, (unsigned)N, rest, counters + 1, h->stream2));
             CU(cudaEventRecord(h->ev_join, h->stream2));
             CU(cudaStreamWaitEvent(s, h->ev_join, 0));
         }
     } else {
-        CU(launch(kc.fn, kc.L, 0u, total, counters, s));
+        CU(launch(kc.fn, threads, smem, kc.L, 0u, total, counters, s));
     }
     return LASSIM_OK;
 }
@@ -572,8 +597,10 @@ int lassim_set_tolerances(lassim_handle *h, double rtol, double atol, long long 
 
 int lassim_set_speculation(lassim_handle *h, int mode) {
     if (!h) return LASSIM_E_INVALID;
-    if (mode < 0 || mode > 2)
-        return fail(h, LASSIM_E_INVALID, "speculation mode %d (0 off, 1 on, 2 auto)", mode);
+    if (mode < 0 || mode > 3)
+        return fail(h, LASSIM_E_INVALID,
+                    "time-series kernel mode %d (0 standard, 1 speculative, 2 auto, 3 stage-parallel)",
+                    mode);
     h->speculate = mode;
     return LASSIM_OK;
 }

@@ -68,7 +68,8 @@ def emit(tb):
     L = []
     w = L.append
     w("// %s: one step attempt of size hs from (y, k1)." % name)
-    w("//   sig(ys, sg)  evaluates the logistic terms sg = sigmoid(W ys) for this lane's genes")
+    w("//   sig(ys, sr, se)  evaluates the logistic terms sigmoid(W ys) = sr + sr*se for this lane's")
+    w("//                genes (reciprocal seed and Newton residual, see logistic_fast_parts)")
     w("//   gmax(x)      max of a non-negative float over the lanes of the group")
     w("// Outputs: yn (the order-%d solution), kn (first stage derivative of the next step);"
       % tb["order"])
@@ -90,7 +91,7 @@ def emit(tb):
     w("        double (&yn)[R], double (&kn)[R]) {")
     decl = ", ".join("%s[R]" % k for k in K[1:S])
     w("    double %s;" % decl)
-    w("    double ys[R], sg[R], q[R], ly[R], cv[R], ef[R], ei[R], yz[R];")
+    w("    double ys[R], sg[R], sr[R], se[R], q[R], ly[R], cv[R], ef[R], ei[R], yz[R];")
     w("#pragma unroll")
     w("    for (int r = 0; r < R; ++r) { ys[r] = fma(hs * %s, k1[r], y[r]); ef[r] = 1.0; ei[r] = 1.0; }" % lit(A[1][0]))
     for s in range(2, S + 1):
@@ -114,10 +115,12 @@ def emit(tb):
         w("            cv[r] = IF ? (hl * vm[r]) * ei[r] : hl * vm[r];")
         w("            q[r] = fma(hl, ly[r], fma(hs, %s, y[r]));" % weighted_sum(row[:s - 1], K[:s - 1], 16))
         w("        }")
-        w("        if constexpr (IF) sig(yz, sg); else sig(ys, sg);")
+        w("        if constexpr (IF) sig(yz, sr, se); else sig(ys, sr, se);")
         w("#pragma unroll")
         w("        for (int r = 0; r < R; ++r) {")
-        w("            %s[r] = fma(cv[r], sg[r], q[r]);" % target)
+        w("            // cv*sigma + q with the Newton step of the reciprocal folded in")
+        w("            %s[r] = fma(cv[r] * sr[r], se[r], fma(cv[r], sr[r], q[r]));" % target)
+        w("            sg[r] = fma(sr[r], se[r], sr[r]);")
         w("            %s[r] = fma(IF ? vm[r] * ei[r] : vm[r], sg[r], ly[r]);" % K[s - 1])
         w("        }")
         w("    }")
@@ -170,13 +173,19 @@ def emit(tb):
         w("    // the estimate needs k1..k%d only: reduce it over the group BEFORE f(yn), so that the" % S)
         w("    // shuffles of the reduction overlap the dependent chain of that last evaluation")
         emit_measure()
-        w("    sig(yn, sg);")
+        w("    sig(yn, sr, se);")
         w("#pragma unroll")
-        w("    for (int r = 0; r < R; ++r) kn[r] = fma(vm[r], sg[r], ly[r]);")
+        w("    for (int r = 0; r < R; ++r) {")
+        w("        kn[r] = fma(vm[r] * sr[r], se[r], fma(vm[r], sr[r], ly[r]));")
+        w("        sg[r] = fma(sr[r], se[r], sr[r]);")
+        w("    }")
     else:
-        w("    sig(yn, sg);")
+        w("    sig(yn, sr, se);")
         w("#pragma unroll")
-        w("    for (int r = 0; r < R; ++r) kn[r] = fma(vm[r], sg[r], ly[r]);")
+        w("    for (int r = 0; r < R; ++r) {")
+        w("        kn[r] = fma(vm[r] * sr[r], se[r], fma(vm[r], sr[r], ly[r]));")
+        w("        sg[r] = fma(sr[r], se[r], sr[r]);")
+        w("    }")
         emit_measure()
     if nE == 1:
         w("    return n0;")
@@ -194,8 +203,9 @@ def main():
     parts = ["// GENERATED by tools/gen_rk_steppers.py - do not edit by hand.",
              "// Fully unrolled step attempts of the explicit Runge-Kutta pairs used by",
              "// grn_cost_kernel.  Every stage state after the second is formed as",
-             "//   ys = fma(hs*a_last*vm, sg, q),  q = y + hs*sum_{older k} + hs*a_last*(-lambda*ys_prev)",
-             "// so only one FMA separates the logistic sg from the next stage state.",
+             "//   ys = c*sigma + q,  c = hs*a_last*vm,  q = y + hs*sum_{older k} + hs*a_last*(-lambda*ys_prev)",
+             "// evaluated as fma(c*sr, se, fma(c, sr, q)) with sigma = sr + sr*se (seed and Newton residual",
+             "// of the reciprocal): two dependent operations from the seed to the next stage state.",
              "#pragma once", "#include <math_constants.h>", "", "namespace lassim {", "",
              "// 1/x for x > 0 from the SFU seed (MUFU.RCP64H) and one Newton step: relative error <= 1e-12",
              "__device__ __forceinline__ double fast_rcp(double x) {",
