@@ -103,7 +103,8 @@ int lassim_set_method(lassim_handle *h, int method);
  *      6 (5) sequential right-hand sides per attempt instead of 12, same
  *      tolerances, weights and norm; steps are also limited so that no logistic
  *      term swings by more than 0.5 inside one (csrc/pirk_kernel.cuh)
- *   2  automatic (default): 3 for batches of at most 2048 candidates, else 0
+ *   2  automatic (default): 3 for batches of at most 2048 candidates, 1 up to
+ *      6144, else 0
  * Results are deterministic for a given mode and batch-size class and stay inside
  * the same error control; the knock-down trajectories always run on the standard
  * kernel.  (No reference counterpart.)  LASSIM_SPECULATE in the environment sets
@@ -258,6 +259,17 @@ int lassim_eval_device_noalloc(lassim_handle *h, int N, const double *dX,
  * current problem dispatches to.  (No reference counterpart.) */
 long long lassim_flops_per_attempt(const lassim_handle *h);
 const char *lassim_kernel_name(lassim_handle *h);
+
+/* The same two for the kernel that integrates the TIME SERIES of a batch of N
+ * candidates under the current lassim_set_speculation mode: equal to the above
+ * when the standard kernel does; twice the flops for speculative attempts (both
+ * halves of the warp work); for the stage-parallel Gauss pair with S stages and
+ * S corrections, (S+1)*S right-hand sides of 2*nnz + 5*n flops plus the stage
+ * sums, predictor and estimate: 60*nnz + 474*n for S = 5.  Attempts of that
+ * kernel are what lassim_last_traj_steps reports in column 0.  (No reference
+ * counterpart.) */
+long long lassim_series_flops_per_attempt(const lassim_handle *h, int N);
+const char *lassim_series_kernel_name(lassim_handle *h, int N);
 
 /* Number of kernels this handle has launched so far (an evaluation is one launch,
  * or two concurrent ones when speculation is active). */

@@ -96,6 +96,10 @@ def load_library():
     lib.lassim_flops_per_attempt.restype = ctypes.c_longlong
     lib.lassim_kernel_name.argtypes = [H]
     lib.lassim_kernel_name.restype = ctypes.c_char_p
+    lib.lassim_series_flops_per_attempt.argtypes = [H, ctypes.c_int]
+    lib.lassim_series_flops_per_attempt.restype = ctypes.c_longlong
+    lib.lassim_series_kernel_name.argtypes = [H, ctypes.c_int]
+    lib.lassim_series_kernel_name.restype = ctypes.c_char_p
     lib.lassim_launch_count.argtypes = [H]
     lib.lassim_launch_count.restype = ctypes.c_longlong
     lib.lassim_last_kernel_ms.argtypes = [H, ctypes.POINTER(ctypes.c_float)]
@@ -193,7 +197,8 @@ class Engine:
     def set_speculation(self, mode="auto"):
         """Kernel for the time-series trajectories: 'off' (the standard one), 'on'
         (speculative half-warp attempts), 'stages' (stage-parallel Gauss pair, one warp
-        per trajectory) or 'auto' ('stages' for batches of at most 2048 candidates)."""
+        per trajectory) or 'auto' ('stages' for batches of at most 2048 candidates, 'on'
+        up to 6144, 'off' beyond)."""
         code = {"off": 0, "on": 1, "auto": 2, "stages": 3, 0: 0, 1: 1, 2: 2, 3: 3,
                 False: 0, True: 1}.get(mode)
         if code is None:
@@ -400,6 +405,13 @@ class Engine:
     @property
     def kernel_name(self):
         return self._lib.lassim_kernel_name(self._h).decode()
+
+    def series_flops_per_attempt(self, N):
+        """Flops per attempt of the kernel that integrates the time series of a batch of N."""
+        return int(self._lib.lassim_series_flops_per_attempt(self._h, int(N)))
+
+    def series_kernel_name(self, N):
+        return self._lib.lassim_series_kernel_name(self._h, int(N)).decode()
 
     @property
     def launch_count(self):

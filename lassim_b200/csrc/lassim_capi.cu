@@ -44,7 +44,7 @@ struct lassim_handle {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr;
     int speculate = 2;        // 0 off, 1 on, 2 auto (small batches)
     bool timed = false;
-    std::string err, kernel_name;
+    std::string err, kernel_name, series_kernel_name;
     long long launches = 0;
 
     // problem (host copies)
@@ -269,19 +269,29 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
 // the time series go to the speculative kernel on the caller's stream (they are the
 // long ones), the other trajectories run concurrently on the auxiliary stream, and
 // `s` waits for both.
+// Which kernel integrates the time series of a batch of N candidates:
+// 0 the standard one, 1 speculative, 3 stage-parallel (lassim_set_speculation).
+// Automatic (2), measured on Th2 populations (tools/gpu_series_sweep.py): the stage-parallel
+// kernel wins up to 2048 candidates (64: 17.6 vs 23.0 vs 30.0 ms for stage-parallel /
+// speculative / standard; 2048: 26.3 / 27.6 / 36.1), the speculative one up to about 6000
+// (4096: 35.8 / 33.7 / 40.5), beyond that the lanes are better spent on more trajectories.
+int series_mode(const lassim_handle *h, const KernelChoice &kc, int N, bool periph) {
+    if (periph) return 0;
+    const bool automatic = h->speculate == 2;
+    if (kc.fn_pirk != nullptr && (h->speculate == 3 || (automatic && N <= 2048))) return 3;
+    if (kc.fn_shadow != nullptr && (h->speculate == 1 || (automatic && N <= 6144))) return 1;
+    return 0;
+}
+
 int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P,
                    const DevBatch &B, int N, int traj_per_candidate, bool periph,
                    cudaStream_t s, unsigned int *counters) {
     // time-series kernel of a small batch: 3 = stage-parallel, 1 = speculative, 2 = auto
     // (stage-parallel where built, for batches of at most 2048 candidates)
-    kernel_fn series_fn = nullptr;
-    if (!periph && kc.fn_pirk != nullptr &&
-        (h->speculate == 3 || (h->speculate == 2 && N <= 2048)))
-        series_fn = kc.fn_pirk;
-    else if (!periph && kc.fn_shadow != nullptr && h->speculate == 1)
-        series_fn = kc.fn_shadow;
+    const int smode = series_mode(h, kc, N, periph);
+    const kernel_fn series_fn = smode == 3 ? kc.fn_pirk : smode == 1 ? kc.fn_shadow : nullptr;
     const bool speculate = series_fn != nullptr;
-    const bool pirk = speculate && series_fn == kc.fn_pirk;
+    const bool pirk = smode == 3;
     auto launch = [&](kernel_fn fn, int threads, size_t smem, int lanes_per_item, unsigned begin,
                       unsigned count, unsigned int *counter, cudaStream_t st) -> cudaError_t {
         if (count == 0) return cudaSuccess;
@@ -620,6 +630,43 @@ long long lassim_flops_per_attempt(const lassim_handle *h) {
     // 8 each in b, e5, e3) + 4 = 24*nnz + 212*n.
     const long long nnz = h->nnz, n = h->n;
     return h->method == kMethodDOP853 ? 24 * nnz + 212 * n : 12 * nnz + 90 * n;
+}
+
+long long lassim_series_flops_per_attempt(const lassim_handle *h, int N) {
+    if (!h || !h->has_problem) return -1;
+    KernelChoice kc;
+    if (!choose_kernel(h, &kc)) return -1;
+    const long long nnz = h->nnz, n = h->n;
+    switch (series_mode(h, kc, N, false)) {
+        case 3: {
+            // S stages, M = S corrections: (M+1)*S RHS evaluations of 2*nnz + 5*n flops,
+            // M*S stage sums and the predictor (2*S flops per gene each), two weighted
+            // sums for solution and estimate (2*S each), 4 for the error measure
+            const long long S = h->n <= 12 ? 5 : 4, M = S;
+            return (M + 1) * S * (2 * nnz + 5 * n) + (M * S + S + 2) * 2 * S * n + 4 * n;
+        }
+        case 1: return 2 * lassim_flops_per_attempt(h);     // both halves of the warp
+        default: return lassim_flops_per_attempt(h);
+    }
+}
+
+const char *lassim_series_kernel_name(lassim_handle *h, int N) {
+    if (!h || !h->has_problem) return "";
+    KernelChoice kc;
+    if (!choose_kernel(h, &kc)) return "";
+    switch (series_mode(h, kc, N, false)) {
+        case 3:
+            h->series_kernel_name = h->n <= 12 ? "grn_series_pirk_kernel<5 Gauss stages x 6 lanes>"
+                                               : "grn_series_pirk_kernel<4 Gauss stages x 8 lanes>";
+            break;
+        case 1:
+            h->series_kernel_name = std::string("grn_cost_kernel<") + kc.name + ", speculative, " +
+                                    (h->method == kMethodDOP853 ? "dop853>" : "dp45>");
+            break;
+        default:
+            h->series_kernel_name = lassim_kernel_name(h);
+    }
+    return h->series_kernel_name.c_str();
 }
 
 const char *lassim_kernel_name(lassim_handle *h) {

@@ -67,10 +67,18 @@ __device__ __forceinline__ double warp_max(double v) {
 
 // stage lines in shared memory per warp: one per LPS lanes of the warp
 __host__ __device__ constexpr int pirk_lines(int LPS) { return (32 + LPS - 1) / LPS; }
-// per warp: derivative lines, state lines (NC + 2 doubles each), logistic values (float2 per lane)
+// doubles between the lines of consecutive stages.  Six lanes per stage: 12, so that the
+// warp's 16-byte stores are contiguous (4 wavefronts instead of 8) while the stages'
+// broadcast loads still fall on different banks; eight lanes per stage: NC + 2, a store
+// is one 128-byte row per stage and the skew keeps the stages' loads apart.
+__host__ __device__ constexpr int pirk_stride(int LPS, int NC) {
+    return (LPS % 8 == 0) ? NC + 2 : 2 * LPS;
+}
+// per warp: derivative lines, state lines, logistic values (float2 per lane)
 constexpr size_t pirk_smem_doubles(int LPS, int NC) {
     return (size_t)kSmemHeader +
-           (size_t)(kPirkThreads / 32) * (2 * pirk_lines(LPS) * (NC + 2) + pirk_lines(LPS) * LPS);
+           (size_t)(kPirkThreads / 32) *
+               (2 * pirk_lines(LPS) * pirk_stride(LPS, NC) + pirk_lines(LPS) * LPS);
 }
 
 template <int S, int LPS, int NC, bool FAST>
@@ -80,7 +88,8 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
     static_assert(S == 4 || S == 5, "predictor polynomial written out for 4 and 5 stages");
     constexpr int R = 2;
     constexpr int M = S;                   // corrections per attempt
-    constexpr int STR = NC + 2;
+    constexpr int STR = pirk_stride(LPS, NC);
+    static_assert(STR >= NC && STR % 2 == 0, "a stage line holds NC doubles, 16-byte aligned");
     constexpr int LINES = pirk_lines(LPS);
     constexpr int PER_WARP = 2 * LINES * STR + LINES * LPS;
     constexpr float kExpo = -1.0f / (2 * S);

@@ -56,7 +56,7 @@ def cost(Y):
     return np.sum((g["data"] - Yf / Yf.max(axis=0)) ** 2 / g["sigma"] ** 2)
 
 
-def pirk(x, s=5, m=5, swing_limit=None, rtol=TOL, atol=TOL, facmax=10.0):
+def pirk(x, s=5, m=5, swing_limit=None, rtol=TOL, atol=TOL, facmax=10.0, safety=0.9, pi_beta=0.0):
     f, sig = system(x)
     order = 2 * s
     A, b, c, polys = gauss(s)
@@ -64,7 +64,7 @@ def pirk(x, s=5, m=5, swing_limit=None, rtol=TOL, atol=TOL, facmax=10.0):
     f0 = f(y)
     h = 0.01 * np.max(np.abs(y) + 1e-6) / max(np.max(np.abs(f0)), 1e-12)
     acc = rej = depth = 0
-    prev = None; ends = []; rejected = False
+    prev = None; ends = []; rejected = False; err_old = 1.0
     for tend in times[1:]:
         while t < tend:
             hs = min(h, tend - t)
@@ -89,11 +89,11 @@ def pirk(x, s=5, m=5, swing_limit=None, rtol=TOL, atol=TOL, facmax=10.0):
                 if swing > swing_limit:
                     err = max(err, (swing / swing_limit) ** order)
             if not np.isfinite(err): err = 1e30
-            fac = facmax if err == 0 else min(facmax, max(0.2, 0.9 * err ** (-1.0 / order)))
+            fac = facmax if err == 0 else min(facmax, max(0.2, safety * err ** (-(1.0 / order - 0.75 * pi_beta)) * err_old ** (-pi_beta)))
             if err <= 1:
                 prev = (y, hs, F); t += hs; y = yn; acc += 1
                 if rejected: fac = min(fac, 1.0)
-                rejected = False; h = hs * fac
+                rejected = False; h = hs * fac; err_old = max(err, 1e-4)
             else:
                 rej += 1; h = hs * min(1.0, fac); rejected = True
         ends.append(y.copy())
