@@ -18,8 +18,8 @@ Prints ONE JSON line (rank 0).  Keys beyond the base contract:
                 compute-bound: ~0.7 KB of HBM traffic per candidate against
                 ~6e7 flops).  achieved = step attempts counted by
                 the kernels x algorithmic flops per attempt (lassim_flops_per_attempt
-                for the knock-down trajectories, lassim_series_flops_per_attempt for
-                the time series) / device time of the evaluation; peak = DFMA
+                for the explicit pair, lassim_series_flops_per_attempt for the attempts
+                of the stage-parallel kernel) / device time of the evaluation; peak = DFMA
                 throughput measured in this run by a register-resident probe
                 kernel (MEASURED_PEAKS.json holds no FP64 figure).
   cpu_baseline  the reference's own compiled Cython functions (oracle/_ref) -
@@ -219,8 +219,8 @@ def run_ours(args):
     eng.set_method(args.method)
     eng.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"], p["pert"], PERT_FACTOR)
     flops_per_attempt = eng.flops_per_attempt      # SURVEY.md 8d, per integrator
-    # the time series of a population this small run on their own kernel (one warp per
-    # trajectory, stage-parallel Gauss pair) with its own attempts and flops per attempt
+    # long time series leave the standard kernel after a cap of attempts and continue in the
+    # stage-parallel Gauss kernel (two warps per trajectory), with its own attempts and flops
     series_flops = eng.series_flops_per_attempt(POP)
 
     dX = torch.from_numpy(X).cuda()
@@ -272,7 +272,7 @@ def run_ours(args):
     barrier()
     launches = eng.launch_count - launches0
     dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
-    series_attempts = int(eng.last_traj_steps(POP)[:, 0].sum())    # of the last step
+    series_attempts = eng.last_stage_parallel_attempts()            # of the last step
     # A knock-down cost is NaN in the reference too when a control end state's rounding-level
     # remnant (1e-190) is negative under a knocked state of 1e120 (-inf/inf after the clip,
     # perturbation_functions.pyx:86-95): every integration must succeed, all but such rows be finite
@@ -309,7 +309,7 @@ def run_ours(args):
         torch.cuda.synchronize()
         ms_sat = eng.last_kernel_ms()
         att = int(dns.view(-1, 3)[:, :2].sum().item())
-        att_series = int(eng.last_traj_steps(POP * reps)[:, 0].sum())
+        att_series = eng.last_stage_parallel_attempts()
         sat_flops = (att - att_series) * flops_per_attempt + \
             att_series * eng.series_flops_per_attempt(POP * reps)
         sat = {"candidates": POP * reps, "kernel_ms": ms_sat,
@@ -370,8 +370,8 @@ def run_ours(args):
                          "time_series_kernel": eng.series_kernel_name(POP),
                          "step_attempts_per_launch": float(np.mean(attempts)),
                          "flops_per_attempt": flops_per_attempt,
-                         "time_series_attempts_per_launch": series_attempts,
-                         "time_series_flops_per_attempt": series_flops,
+                         "stage_parallel_attempts_per_launch": series_attempts,
+                         "stage_parallel_flops_per_attempt": series_flops,
                          "peak_source": "in-run DFMA probe kernel (MEASURED_PEAKS.json has "
                                         "HBM and bf16 figures only)",
                          "machine_full": dict(sat, frac=sat["achieved_tflops"] / fp64_peak,

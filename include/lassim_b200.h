@@ -91,25 +91,39 @@ enum { LASSIM_METHOD_DP45 = 0, LASSIM_METHOD_DOP853 = 1 };
 int lassim_set_method(lassim_handle *h, int method);
 
 /* Kernel for the time-series trajectories of problems of at most 16 genes.  A
- * small batch waits for its longest time series, so these modes trade lanes for
- * fewer SEQUENTIAL right-hand sides on that trajectory (one warp per trajectory):
+ * small batch waits for its longest time series (a limit cycle needs 15,000+
+ * step attempts where most candidates need 600), so these modes trade lanes for
+ * fewer SEQUENTIAL right-hand sides on such trajectories:
  *   0  the standard kernel (16 lanes per trajectory, the pair lassim_set_method names)
- *   1  speculative attempts: every attempt is made at the proposed step size and,
- *      by the other half of the warp, at 0.7 of it; when the full step fails its
- *      error test and the shorter one passes, the shorter one is accepted
- *      instead of starting over (a fifth fewer sequential attempts on limit cycles)
- *   3  stage-parallel: a 5-stage Gauss collocation pair (4-stage above 12 genes)
- *      solved by fixed-point iteration with its stages side by side in the warp,
- *      6 (5) sequential right-hand sides per attempt instead of 12, same
- *      tolerances, weights and norm; steps are also limited so that no logistic
- *      term swings by more than 0.5 inside one (csrc/pirk_kernel.cuh)
- *   2  automatic (default): 3 for batches of at most 2048 candidates, 1 up to
- *      6144, else 0
- * Results are deterministic for a given mode and batch-size class and stay inside
- * the same error control; the knock-down trajectories always run on the standard
- * kernel.  (No reference counterpart.)  LASSIM_SPECULATE in the environment sets
- * the initial mode. */
+ *   1  speculative attempts: one warp per time series; every attempt is made at the
+ *      proposed step size and, by the other half of the warp, at 0.7 of it; when
+ *      the full step fails its error test and the shorter one passes, the shorter
+ *      one is accepted instead of starting over
+ *   3  stage-parallel: one warp per time series; a 5-stage Gauss collocation pair
+ *      (4-stage above 12 genes) solved by fixed-point iteration with its stages
+ *      side by side in the warp, 6 (5) sequential right-hand sides per attempt
+ *      instead of 12, same tolerances, weights and norm; steps are also limited so
+ *      that no logistic term swings by more than 0.5 inside one (csrc/pirk_kernel.cuh)
+ *   4  the same with a second warp attempting 0.7 of every step (as in 1)
+ *   5  hand-over: every time series starts in the standard kernel; those still
+ *      going after a cap of attempts (three per four candidates of the batch, within
+ *      [500, 8000]; LASSIM_SERIES_CAP in the environment overrides) stop at the
+ *      step they are on and continue in kernel 4, launched behind it on the same
+ *      stream.  The many short time series stay cheap, the few long ones get the
+ *      fast kernel almost to themselves
+ *   2  automatic (default): 5 for batches of at most 16,384 candidates, else 0
+ * Results are deterministic for a given mode and batch size and stay inside the
+ * same error control; with 5 a candidate's time series depends on the batch size
+ * through the cap (at the level of the integration tolerance).  The knock-down
+ * trajectories always run on the standard kernel, concurrently on a second
+ * stream.  (No reference counterpart.)  LASSIM_SPECULATE in the environment
+ * sets the initial mode. */
 int lassim_set_speculation(lassim_handle *h, int mode);
+
+/* Attempts a time series makes in the standard kernel before mode 5 hands it
+ * over; 0 (default) = automatic, three per four candidates of the batch within
+ * [500, 8000].  (No reference counterpart.) */
+int lassim_set_series_cap(lassim_handle *h, unsigned int attempts);
 
 /* Current decision-vector length (2n + nnz), trajectories per candidate
  * (1 + unique time pairs + n when a knock-down matrix is set, else 1). */
@@ -265,11 +279,17 @@ const char *lassim_kernel_name(lassim_handle *h);
  * when the standard kernel does; twice the flops for speculative attempts (both
  * halves of the warp work); for the stage-parallel Gauss pair with S stages and
  * S corrections, (S+1)*S right-hand sides of 2*nnz + 5*n flops plus the stage
- * sums, predictor and estimate: 60*nnz + 474*n for S = 5.  Attempts of that
- * kernel are what lassim_last_traj_steps reports in column 0.  (No reference
+ * sums, predictor and estimate: 60*nnz + 474*n for S = 5, twice that when two
+ * warps work (modes 4 and 5).  (No reference
  * counterpart.) */
 long long lassim_series_flops_per_attempt(const lassim_handle *h, int N);
 const char *lassim_series_kernel_name(lassim_handle *h, int N);
+
+/* Attempts made by the stage-parallel kernel in the last evaluation, summed over
+ * its trajectories (with mode 5 a time series makes its first attempts in the
+ * standard kernel; lassim_last_traj_steps reports the sum of both).  Blocks until
+ * the evaluation has finished.  (No reference counterpart.) */
+int lassim_last_stage_parallel_attempts(lassim_handle *h, unsigned long long *attempts);
 
 /* Number of kernels this handle has launched so far (an evaluation is one launch,
  * or two concurrent ones when speculation is active). */

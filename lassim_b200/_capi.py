@@ -53,6 +53,8 @@ def load_library():
                                           ctypes.c_longlong]
     lib.lassim_set_speculation.argtypes = [H, ctypes.c_int]
     lib.lassim_set_speculation.restype = ctypes.c_int
+    lib.lassim_set_series_cap.argtypes = [H, ctypes.c_uint]
+    lib.lassim_set_series_cap.restype = ctypes.c_int
     lib.lassim_set_method.argtypes = [H, ctypes.c_int]
     lib.lassim_set_method.restype = ctypes.c_int
     lib.lassim_dim.argtypes = [H]
@@ -100,6 +102,8 @@ def load_library():
     lib.lassim_series_flops_per_attempt.restype = ctypes.c_longlong
     lib.lassim_series_kernel_name.argtypes = [H, ctypes.c_int]
     lib.lassim_series_kernel_name.restype = ctypes.c_char_p
+    lib.lassim_last_stage_parallel_attempts.argtypes = [H, c_ull_p]
+    lib.lassim_last_stage_parallel_attempts.restype = ctypes.c_int
     lib.lassim_launch_count.argtypes = [H]
     lib.lassim_launch_count.restype = ctypes.c_longlong
     lib.lassim_last_kernel_ms.argtypes = [H, ctypes.POINTER(ctypes.c_float)]
@@ -197,14 +201,20 @@ class Engine:
     def set_speculation(self, mode="auto"):
         """Kernel for the time-series trajectories: 'off' (the standard one), 'on'
         (speculative half-warp attempts), 'stages' (stage-parallel Gauss pair, one warp
-        per trajectory) or 'auto' ('stages' for batches of at most 2048 candidates, 'on'
-        up to 6144, 'off' beyond)."""
-        code = {"off": 0, "on": 1, "auto": 2, "stages": 3, 0: 0, 1: 1, 2: 2, 3: 3,
-                False: 0, True: 1}.get(mode)
+        per trajectory), 'stages2' (the same with a second warp attempting a shorter step),
+        'handover' (standard kernel first, long time series continue in 'stages2') or 'auto'
+        ('handover' up to 16,384 candidates, 'off' beyond)."""
+        code = {"off": 0, "on": 1, "auto": 2, "stages": 3, "stages2": 4, "handover": 5,
+                0: 0, 1: 1, 2: 2, 3: 3, 4: 4, 5: 5, False: 0, True: 1}.get(mode)
         if code is None:
             raise ValueError("time-series kernel mode %r (use 'off', 'on', 'stages' or 'auto')"
                              % (mode,))
         self._check(self._lib.lassim_set_speculation(self._h, code), "lassim_set_speculation")
+
+    def set_series_cap(self, attempts=0):
+        """Attempts a time series makes in the standard kernel before 'handover' moves it
+        to the stage-parallel kernel; 0 = automatic."""
+        self._check(self._lib.lassim_set_series_cap(self._h, int(attempts)), "lassim_set_series_cap")
 
     def set_method(self, method="dop853"):
         """'dop853' (Dormand-Prince 8(5,3), default) or 'dp45' (Dormand-Prince 5(4))."""
@@ -409,6 +419,13 @@ class Engine:
     def series_flops_per_attempt(self, N):
         """Flops per attempt of the kernel that integrates the time series of a batch of N."""
         return int(self._lib.lassim_series_flops_per_attempt(self._h, int(N)))
+
+    def last_stage_parallel_attempts(self):
+        """Attempts the stage-parallel kernel made in the last evaluation (sum)."""
+        v = ctypes.c_ulonglong()
+        self._check(self._lib.lassim_last_stage_parallel_attempts(self._h, ctypes.byref(v)),
+                    "lassim_last_stage_parallel_attempts")
+        return int(v.value)
 
     def series_kernel_name(self, N):
         return self._lib.lassim_series_kernel_name(self._h, int(N)).decode()

@@ -74,6 +74,16 @@ struct DevBatch {
     const int *pgene;         // [N] peripheral gene of each candidate (PERIPH kernels)
     unsigned int work_begin;  // this launch serves work items [work_begin, work_begin + work_count)
     unsigned int work_count;  //   of the N*K items (item w: trajectory w / N of candidate w % N)
+    // Hand-over of long time series (see launch_kernels): with series_cap > 0 a time series
+    // that has used that many attempts stops at the step it is on, leaves its state behind
+    // (y in the last row of its Y block, t in cost_main, h in pert_cost) and appends
+    // (sample index << 32 | candidate) to long_list; the stage-parallel kernel launched
+    // behind it with resume = 1 takes its work items from that list.
+    unsigned int series_cap = 0;
+    int resume = 0;
+    unsigned int *long_count = nullptr;        // zeroed before launch
+    unsigned long long *long_list = nullptr;   // [N]
+    unsigned long long *sp_attempts = nullptr; // attempts made by the stage-parallel kernel (sum)
 };
 
 #ifndef LASSIM_FACMAX
@@ -714,9 +724,25 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
             }
         }
 
-        if (active && ti >= nt) {
+        // a time series over its attempt cap is handed to the kernel behind this one
+        bool handover = false;
+        if constexpr (!PERIPH && !SHADOW)
+            handover = active && k == 0 && B.series_cap != 0u && ti < nt && st == 0 &&
+                       nacc + nrej >= B.series_cap;
+        if (active && (ti >= nt || handover)) {
             // ------------------------------------------------------ epilogue
-            if (k == 0) {
+            if (handover) {
+                double *Yl = B.Y + ((size_t)c * P.T + (P.T - 1)) * n;
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    if (gene_ok[r] && writer) Yl[lg * R + r] = y[r];
+                if (lg == 0 && writer) {
+                    B.cost_main[c] = t;
+                    B.pert_cost[c] = h;
+                    B.long_list[atomicAdd(B.long_count, 1u)] =
+                        ((unsigned long long)(unsigned)ti << 32) | (unsigned long long)(unsigned)c;
+                }
+            } else if (k == 0) {
                 const double *Yc = B.Y + (size_t)c * P.T * n;
                 double part = 0.0;
 #pragma unroll
@@ -767,7 +793,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
             for (int r = 0; r < R; ++r) { y[r] = 0.0; k1[r] = 0.0; gr[r] = 0.0; }
             grow = false;
             h = 0.0; t = 0.0; tend = 0.0;
-            if (B.mode == 0) {
+            if (B.mode == 0 && !handover) {
                 __threadfence();
                 if constexpr (SHADOW) __syncwarp(); else G::sync_group(gmask);
                 unsigned old = 0;

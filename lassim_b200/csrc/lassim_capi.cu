@@ -42,7 +42,8 @@ struct lassim_handle {
     int sm_count = 0;
     cudaStream_t stream = nullptr, stream2 = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr;
-    int speculate = 2;        // 0 off, 1 on, 2 auto (small batches)
+    int speculate = 2;        // lassim_set_speculation mode (2 = automatic)
+    unsigned series_cap = 0;      // hand-over cap; 0 = automatic (series_cap_for)
     bool timed = false;
     std::string err, kernel_name, series_kernel_name;
     long long launches = 0;
@@ -70,6 +71,7 @@ struct lassim_handle {
     DevBuf<double> d_X, d_cost, d_cost_main, d_pert_cost, d_Y, d_E, d_probe;
     DevBuf<unsigned char> d_zero;   // work counter | done | status | counters
     DevBuf<unsigned int> d_steps;
+    DevBuf<unsigned long long> d_long;   // hand-over list of long time series
     int last_N = 0;
     bool last_had_E = false;
 
@@ -154,7 +156,7 @@ struct ZeroLayout {
 
 ZeroLayout zero_layout(int N) {
     ZeroLayout z;
-    z.off_done = 16;
+    z.off_done = 32;       // [0,16): work counters and hand-over count, [16,24): stage-parallel attempts
     z.off_status = z.off_done + sizeof(int) * (size_t)N;
     z.off_counters = (z.off_status + sizeof(int) * (size_t)N + 15) & ~(size_t)15;
     z.bytes = z.off_counters + sizeof(unsigned long long) * 3 * (size_t)N;
@@ -170,6 +172,8 @@ struct KernelChoice {
     kernel_fn fn_shadow = nullptr;   // warp-per-trajectory speculative variant, if built
     kernel_fn fn_pirk = nullptr;     // warp-per-trajectory stage-parallel variant, if built
     size_t pirk_smem = 0;
+    kernel_fn fn_pirk2 = nullptr;    // the same with a second warp attempting a shorter step
+    size_t pirk2_smem = 0;
 };
 
 // dynamic shared memory of one CTA: header (2^(j/256) table, reduction scratch)
@@ -197,10 +201,14 @@ kernel_fn shadow_kernel(int method) {
 void pirk_kernel(int n, KernelChoice *out) {
     if (n <= 12) {
         out->fn_pirk = grn_series_pirk_kernel<5, 6, 12, true>;
-        out->pirk_smem = pirk_smem_doubles(6, 12) * sizeof(double);
+        out->pirk_smem = pirk_smem_doubles(5, 6, 12, false) * sizeof(double);
+        out->fn_pirk2 = grn_series_pirk_kernel<5, 6, 12, true, true>;
+        out->pirk2_smem = pirk_smem_doubles(5, 6, 12, true) * sizeof(double);
     } else {
         out->fn_pirk = grn_series_pirk_kernel<4, 8, 16, true>;
-        out->pirk_smem = pirk_smem_doubles(8, 16) * sizeof(double);
+        out->pirk_smem = pirk_smem_doubles(4, 8, 16, false) * sizeof(double);
+        out->fn_pirk2 = grn_series_pirk_kernel<4, 8, 16, true, true>;
+        out->pirk2_smem = pirk_smem_doubles(4, 8, 16, true) * sizeof(double);
     }
 }
 
@@ -271,16 +279,36 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
 // `s` waits for both.
 // Which kernel integrates the time series of a batch of N candidates:
 // 0 the standard one, 1 speculative, 3 stage-parallel (lassim_set_speculation).
-// Automatic (2), measured on Th2 populations (tools/gpu_series_sweep.py): the stage-parallel
-// kernel wins up to 2048 candidates (64: 17.6 vs 23.0 vs 30.0 ms for stage-parallel /
-// speculative / standard; 2048: 26.3 / 27.6 / 36.1), the speculative one up to about 6000
-// (4096: 35.8 / 33.7 / 40.5), beyond that the lanes are better spent on more trajectories.
+// Automatic (2): hand-over (5) wherever the stage-parallel kernel exists (n <= 16) up to 16,384
+// candidates, the standard kernel alone beyond.  Measured on Th2 populations
+// (tools/gpu_series_sweep.py, tools/gpu_handover_sweep.py; ms per evaluation):
+//        N   standard  speculative  stage-par.  st.-par. x2   hand-over (cap)
+//       64     30.8       23.0        17.5        14.3        14.8  (500)
+//      256     31.1       23.3        19.0        17.2        16.8  (500)
+//     1024     35.2       25.8        22.6-24.1   23.1-24.1   22.0  (500-2000)
+//     4096     41.1       33.5        35.8        46.0        29.7  (4000)
+//     8192     49.7       47.4        54.3        78.5        41.6  (8000)
+//    16384     69.6        -           -           -          65.7  (4000)
+//    65536    176.4        -           -           -         193.4  (8000)
 int series_mode(const lassim_handle *h, const KernelChoice &kc, int N, bool periph) {
     if (periph) return 0;
     const bool automatic = h->speculate == 2;
-    if (kc.fn_pirk != nullptr && (h->speculate == 3 || (automatic && N <= 2048))) return 3;
-    if (kc.fn_shadow != nullptr && (h->speculate == 1 || (automatic && N <= 6144))) return 1;
+    if (kc.fn_pirk2 != nullptr && (h->speculate == 5 || (automatic && N <= 16384))) return 5;
+    if (kc.fn_pirk2 != nullptr && h->speculate == 4) return 4;
+    if (kc.fn_pirk != nullptr && h->speculate == 3) return 3;
+    if (kc.fn_shadow != nullptr && h->speculate == 1) return 1;
     return 0;
+}
+
+// Attempts a time series gets in the standard kernel before it is handed over: enough that
+// the many short ones finish there (their hand-over would crowd the stage-parallel kernel),
+// few enough that the long ones lose little time at the slower pace.  Measured optimum
+// (table above; 1024 candidates: 300 -> 23.8 ms, 500 -> 22.9, 750 -> 22.5, 1000 -> 22.8,
+// 1500 -> 23.4, 3000 -> 26.4, medians): three attempts per four candidates, within [500, 8000].
+unsigned series_cap_for(const lassim_handle *h, int N) {
+    if (h->series_cap != 0u) return h->series_cap;
+    const long long c = 3LL * N / 4;
+    return (unsigned)(c < 500 ? 500 : c > 8000 ? 8000 : c);
 }
 
 int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P,
@@ -289,11 +317,12 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
     // time-series kernel of a small batch: 3 = stage-parallel, 1 = speculative, 2 = auto
     // (stage-parallel where built, for batches of at most 2048 candidates)
     const int smode = series_mode(h, kc, N, periph);
-    const kernel_fn series_fn = smode == 3 ? kc.fn_pirk : smode == 1 ? kc.fn_shadow : nullptr;
+    const kernel_fn series_fn = smode >= 4 ? kc.fn_pirk2 : smode == 3 ? kc.fn_pirk
+                              : smode == 1 ? kc.fn_shadow : nullptr;
     const bool speculate = series_fn != nullptr;
-    const bool pirk = smode == 3;
     auto launch = [&](kernel_fn fn, int threads, size_t smem, int lanes_per_item, unsigned begin,
-                      unsigned count, unsigned int *counter, cudaStream_t st) -> cudaError_t {
+                      unsigned count, unsigned int *counter, cudaStream_t st,
+                      unsigned series_cap = 0u, int resume = 0) -> cudaError_t {
         if (count == 0) return cudaSuccess;
         const int items_per_cta = threads / lanes_per_item;
         cudaError_t e = cudaFuncSetAttribute((const void *)fn,
@@ -309,6 +338,8 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
         if (blocks < 1) blocks = 1;
         DevBatch Bl = B;
         Bl.work_begin = begin; Bl.work_count = count; Bl.work_counter = counter;
+        Bl.series_cap = series_cap; Bl.resume = resume; Bl.long_count = counters + 2;
+        Bl.sp_attempts = reinterpret_cast<unsigned long long *>(counters + 4);
         fn<<<(unsigned)blocks, threads, smem, st>>>(P, Bl);
         h->launches += 1;
         return cudaGetLastError();
@@ -322,8 +353,18 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
             CU(cudaEventRecord(h->ev_fork, s));
             CU(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
         }
-        if (pirk) CU(launch(series_fn, kPirkThreads, kc.pirk_smem, 32, 0u, (unsigned)N, counters, s));
-        else CU(launch(series_fn, threads, smem, 32, 0u, (unsigned)N, counters, s));
+        if (smode == 5) {
+            // every time series starts in the standard kernel; the ones still going after
+            // series_cap attempts continue in the two-warp stage-parallel kernel behind it
+            CU(launch(kc.fn, threads, smem, kc.L, 0u, (unsigned)N, counters, s, series_cap_for(h, N), 0));
+            CU(launch(kc.fn_pirk2, kPirkThreads, kc.pirk2_smem, 64, 0u, (unsigned)N, counters + 3, s,
+                      0u, 1));
+        } else if (smode == 4)
+            CU(launch(series_fn, kPirkThreads, kc.pirk2_smem, 64, 0u, (unsigned)N, counters, s));
+        else if (smode == 3)
+            CU(launch(series_fn, kPirkThreads, kc.pirk_smem, 32, 0u, (unsigned)N, counters, s));
+        else
+            CU(launch(series_fn, threads, smem, 32, 0u, (unsigned)N, counters, s));
         if (rest > 0) {
             CU(launch(kc.fn, threads, smem, kc.L, (unsigned)N, rest, counters + 1, h->stream2));
             CU(cudaEventRecord(h->ev_join, h->stream2));
@@ -383,6 +424,7 @@ int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
     CU(h->d_cost_main.reserve(N));
     CU(h->d_pert_cost.reserve(N));
     CU(h->d_steps.reserve((size_t)N * K));
+    CU(h->d_long.reserve((size_t)N));
     if (!dY) {
         CU(h->d_Y.reserve((size_t)N * h->T * n));
         dY = h->d_Y.p;
@@ -414,6 +456,7 @@ int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
     B.status = reinterpret_cast<int *>(h->d_zero.p + z.off_status);
     B.counters = reinterpret_cast<unsigned long long *>(h->d_zero.p + z.off_counters);
     B.Y = dY; B.E = h->d_E.p; B.traj_steps = h->d_steps.p; B.order = nullptr;
+    B.long_list = h->d_long.p;
 
     CU(cudaEventRecord(h->ev0, s));
     int rc = launch_kernels(h, kc, P, B, N, mode == 0 ? K : 1, periph, s,
@@ -474,6 +517,7 @@ int lassim_create(int device, lassim_handle **out) {
         return fail(nullptr, LASSIM_E_CUDA, "stream/event creation failed");
     }
     if (const char *sp = getenv("LASSIM_SPECULATE")) h->speculate = atoi(sp);
+    if (const char *sp = getenv("LASSIM_SERIES_CAP")) h->series_cap = (unsigned)atoi(sp);
     double tab[kExpTable];
     for (int j = 0; j < kExpTable; ++j) tab[j] = exp2((double)j / (double)kExpTable);
     if (cudaMemcpyToSymbol(c_exp2_table, tab, sizeof(tab)) != cudaSuccess) {
@@ -499,7 +543,7 @@ int lassim_destroy(lassim_handle *h) {
     h->d_traj_prefix.release(); h->d_knock_ctrl.release();
     h->d_X.release(); h->d_cost.release(); h->d_cost_main.release();
     h->d_pert_cost.release(); h->d_Y.release(); h->d_E.release(); h->d_probe.release();
-    h->d_zero.release(); h->d_steps.release();
+    h->d_zero.release(); h->d_steps.release(); h->d_long.release();
     cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
     cudaEventDestroy(h->ev_fork); cudaEventDestroy(h->ev_join);
     cudaStreamDestroy(h->stream2);
@@ -605,12 +649,18 @@ int lassim_set_tolerances(lassim_handle *h, double rtol, double atol, long long 
     return LASSIM_OK;
 }
 
+int lassim_set_series_cap(lassim_handle *h, unsigned int attempts) {
+    if (!h) return LASSIM_E_INVALID;
+    h->series_cap = attempts;
+    return LASSIM_OK;
+}
+
 int lassim_set_speculation(lassim_handle *h, int mode) {
     if (!h) return LASSIM_E_INVALID;
-    if (mode < 0 || mode > 3)
+    if (mode < 0 || mode > 5)
         return fail(h, LASSIM_E_INVALID,
-                    "time-series kernel mode %d (0 standard, 1 speculative, 2 auto, 3 stage-parallel)",
-                    mode);
+                    "time-series kernel mode %d (0 standard, 1 speculative, 2 auto, 3 stage-parallel, "
+                    "4 stage-parallel + speculative)", mode);
     h->speculate = mode;
     return LASSIM_OK;
 }
@@ -637,27 +687,46 @@ long long lassim_series_flops_per_attempt(const lassim_handle *h, int N) {
     KernelChoice kc;
     if (!choose_kernel(h, &kc)) return -1;
     const long long nnz = h->nnz, n = h->n;
-    switch (series_mode(h, kc, N, false)) {
-        case 3: {
+    const int smode = series_mode(h, kc, N, false);
+    switch (smode) {
+        case 3:
+        case 4:
+        case 5: {
             // S stages, M = S corrections: (M+1)*S RHS evaluations of 2*nnz + 5*n flops,
             // M*S stage sums and the predictor (2*S flops per gene each), two weighted
             // sums for solution and estimate (2*S each), 4 for the error measure
             const long long S = h->n <= 12 ? 5 : 4, M = S;
-            return (M + 1) * S * (2 * nnz + 5 * n) + (M * S + S + 2) * 2 * S * n + 4 * n;
+            const long long one = (M + 1) * S * (2 * nnz + 5 * n) + (M * S + S + 2) * 2 * S * n + 4 * n;
+            return smode >= 4 ? 2 * one : one;      // 4, 5: both warps of the pair work
         }
         case 1: return 2 * lassim_flops_per_attempt(h);     // both halves of the warp
         default: return lassim_flops_per_attempt(h);
     }
 }
 
+int lassim_last_stage_parallel_attempts(lassim_handle *h, unsigned long long *attempts) {
+    if (!h || !attempts) return LASSIM_E_INVALID;
+    if (!h->timed || !h->d_zero.p) return fail(h, LASSIM_E_STATE, "no evaluation has run yet");
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(attempts, h->d_zero.p + 16, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    return LASSIM_OK;
+}
+
 const char *lassim_series_kernel_name(lassim_handle *h, int N) {
     if (!h || !h->has_problem) return "";
     KernelChoice kc;
     if (!choose_kernel(h, &kc)) return "";
-    switch (series_mode(h, kc, N, false)) {
+    const int smode = series_mode(h, kc, N, false);
+    switch (smode) {
         case 3:
-            h->series_kernel_name = h->n <= 12 ? "grn_series_pirk_kernel<5 Gauss stages x 6 lanes>"
-                                               : "grn_series_pirk_kernel<4 Gauss stages x 8 lanes>";
+        case 4:
+        case 5:
+            h->series_kernel_name = std::string(h->n <= 12 ? "grn_series_pirk_kernel<5 Gauss stages x 6 lanes"
+                                                            : "grn_series_pirk_kernel<4 Gauss stages x 8 lanes") +
+                                    (smode >= 4 ? ", two step sizes>" : ">") +
+                                    (smode == 5 ? " behind " + std::string(lassim_kernel_name(h)) : "");
             break;
         case 1:
             h->series_kernel_name = std::string("grn_cost_kernel<") + kc.name + ", speculative, " +
@@ -1088,21 +1157,22 @@ namespace {
 
 struct NoallocLayout {
     size_t off_done, off_status, off_counters, zero_bytes;
-    size_t off_cost_main, off_pert_cost, off_steps, off_Y, off_E, bytes;
+    size_t off_cost_main, off_pert_cost, off_steps, off_long, off_Y, off_E, bytes;
 };
 
 size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 NoallocLayout noalloc_layout(int N, int T, int K, int n) {
     NoallocLayout L;
-    L.off_done = 16;                                       // [0,16): work counter
+    L.off_done = 32;                                       // [0,32): work counters, hand-over count, attempts
     L.off_status = L.off_done + sizeof(int) * (size_t)N;
     L.off_counters = (L.off_status + sizeof(int) * (size_t)N + 15) & ~(size_t)15;
     L.zero_bytes = L.off_counters + sizeof(unsigned long long) * 3 * (size_t)N;
     L.off_cost_main = align256(L.zero_bytes);
     L.off_pert_cost = align256(L.off_cost_main + sizeof(double) * (size_t)N);
     L.off_steps = align256(L.off_pert_cost + sizeof(double) * (size_t)N);
-    L.off_Y = align256(L.off_steps + sizeof(unsigned) * (size_t)N * K);
+    L.off_long = align256(L.off_steps + sizeof(unsigned) * (size_t)N * K);
+    L.off_Y = align256(L.off_long + sizeof(unsigned long long) * (size_t)N);
     L.off_E = align256(L.off_Y + sizeof(double) * (size_t)N * T * n);
     L.bytes = L.off_E + sizeof(double) * (size_t)N * K * n;
     return L;
@@ -1124,7 +1194,7 @@ extern "C" int lassim_eval_device_noalloc(lassim_handle *h, int N, const double 
     const int K = h->K, n = h->n, T = h->T;
     const NoallocLayout L = noalloc_layout(N, T, K, n);
     if (L.bytes > (size_t)LASSIM_NOALLOC_SCRATCH_BYTES) {
-        const size_t per = 8 * ((size_t)T * n + (size_t)K * n) + 4 * (size_t)K + 56;
+        const size_t per = 8 * ((size_t)T * n + (size_t)K * n) + 4 * (size_t)K + 64;
         return fail(h, LASSIM_E_INVALID,
                     "eval_device_noalloc: %d candidates of this problem need %zu bytes of "
                     "scratch but the built-in scratch holds %u bytes (about %zu candidates); "
@@ -1178,6 +1248,7 @@ extern "C" int lassim_eval_device_noalloc(lassim_handle *h, int N, const double 
     B.Y = reinterpret_cast<double *>(base + L.off_Y);
     B.E = reinterpret_cast<double *>(base + L.off_E);
     B.order = nullptr;
+    B.long_list = reinterpret_cast<unsigned long long *>(base + L.off_long);
 
     // same kernels, same speculation policy as lassim_eval_device: same costs
     int rc = launch_kernels(h, kc, P, B, N, K, false, s, reinterpret_cast<unsigned int *>(base));

@@ -74,14 +74,27 @@ __host__ __device__ constexpr int pirk_lines(int LPS) { return (32 + LPS - 1) / 
 __host__ __device__ constexpr int pirk_stride(int LPS, int NC) {
     return (LPS % 8 == 0) ? NC + 2 : 2 * LPS;
 }
-// per warp: derivative lines, state lines, logistic values (float2 per lane)
-constexpr size_t pirk_smem_doubles(int LPS, int NC) {
+// DUAL: doubles of one exchange slot of a warp pair (solution + derivatives of every lane,
+// error measure and step factor), S stages
+__host__ __device__ constexpr int pirk_slot(int S) { return 32 * 2 * (S + 1) + 2; }
+// per warp: derivative lines, state lines, logistic values (float2 per lane);
+// DUAL adds, per pair of warps, 2 (parity) x 2 (role) exchange slots and a work-item slot
+constexpr size_t pirk_smem_doubles(int S, int LPS, int NC, bool dual) {
     return (size_t)kSmemHeader +
            (size_t)(kPirkThreads / 32) *
-               (2 * pirk_lines(LPS) * pirk_stride(LPS, NC) + pirk_lines(LPS) * LPS);
+               (2 * pirk_lines(LPS) * pirk_stride(LPS, NC) + pirk_lines(LPS) * LPS) +
+           (dual ? (size_t)(kPirkThreads / 64) * (4 * pirk_slot(S) + 2) : 0);
 }
 
-template <int S, int LPS, int NC, bool FAST>
+// Step ratio of the second warp of a pair (DUAL), as in the speculative explicit kernel.
+constexpr double kPirkShadowRatio = 0.7;
+
+// DUAL: two warps per trajectory.  Both carry the same state; warp 0 of the pair attempts
+// the proposed step, warp 1 the same step from the same state at 0.7 of the size, and when
+// the full step fails its test while the shorter one passes, the shorter one is taken instead
+// of starting over (a limit cycle rejects 17-25 % of its attempts).  One exchange through
+// shared memory and one named barrier per attempt; the warps sit on different schedulers.
+template <int S, int LPS, int NC, bool FAST, bool DUAL = false>
 __global__ void __launch_bounds__(kPirkThreads, 2)
 grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
     static_assert(S * LPS <= 32 && 2 * LPS <= NC + 3, "stages x lanes must fit one warp");
@@ -104,6 +117,18 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
     double *fline = smem + kSmemHeader + wid * PER_WARP;
     double *yline = fline + LINES * STR;
     float2 *sline = reinterpret_cast<float2 *>(yline + LINES * STR);
+    // warp pair (DUAL): role 0 attempts the proposed step, role 1 the shorter one
+    const int pairq = wid >> 1, role = DUAL ? (wid & 1) : 0;
+    constexpr int SLOT = pirk_slot(S);
+    double *xch = smem + kSmemHeader + (kPirkThreads / 32) * PER_WARP + pairq * (4 * SLOT + 2);
+    unsigned *work_slot = reinterpret_cast<unsigned *>(xch + 4 * SLOT);
+    int par = 0;
+    auto pair_barrier = [&]() {
+        if constexpr (DUAL) {          // literal ids: the kernel reserves 3 barriers, not all 16
+            if (pairq == 0) asm volatile("bar.sync 1, 64;" ::: "memory");
+            else asm volatile("bar.sync 2, 64;" ::: "memory");
+        }
+    };
     fill_exp2_table(tab);
     for (int i = lane; i < PER_WARP; i += 32) fline[i] = 0.0;
     __syncthreads();
@@ -130,7 +155,7 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
     bool gene_ok[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) gene_ok[r] = staged && (2 * l + r) < n;
-    const bool writer = stage == 0;
+    const bool writer = stage == 0 && role == 0;
 
     DenseW<R, NC> wts;
     double y[R], lam[R], vm[R], Fp[S][R];
@@ -183,11 +208,27 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
 
     while (true) {
         unsigned w = 0;
-        if (lane == 0) w = atomicAdd(B.work_counter, 1u);
-        w = __shfl_sync(0xffffffffu, w, 0);
-        if (w >= B.work_count) break;
-        w += B.work_begin;
-        if (B.order != nullptr) w = B.order[w];
+        if constexpr (DUAL) {
+            if (role == 0 && lane == 0) *work_slot = atomicAdd(B.work_counter, 1u);
+            pair_barrier();
+            w = *work_slot;
+            pair_barrier();            // both have read it before the next item overwrites it
+        } else {
+            if (lane == 0) w = atomicAdd(B.work_counter, 1u);
+            w = __shfl_sync(0xffffffffu, w, 0);
+        }
+        // resume: the work items are the time series the kernel ahead of this one handed over
+        const unsigned work_count = B.resume ? __ldcg(B.long_count) : B.work_count;
+        if (w >= work_count) break;
+        int resume_ti = 0;
+        if (B.resume) {
+            const unsigned long long e = __ldcg(B.long_list + w);
+            w = (unsigned)(e & 0xffffffffull);
+            resume_ti = (int)(e >> 32);
+        } else {
+            w += B.work_begin;
+            if (B.order != nullptr) w = B.order[w];
+        }
         const int c = (int)w;                      // time series: item w is candidate w
         const double *x = B.X + (size_t)c * P.dim;
 #pragma unroll
@@ -205,9 +246,23 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
         int left = (nt < 2) ? 0 : nt - 1;          // sample times still to reach
         bool rejected = false;
         double *Yc = B.Y + (size_t)c * P.T * n;
+        double h_resume = 0.0;
+        if (B.resume) {
+            // state left by the hand-over: y in the last sample row, t and h in the cost slots
+            const double *Yl = Yc + (size_t)(P.T - 1) * n;
 #pragma unroll
-        for (int r = 0; r < R; ++r)
-            if (gene_ok[r] && writer) Yc[2 * l + r] = y[r];
+            for (int r = 0; r < R; ++r)
+                if (gene_ok[r]) y[r] = __ldcg(Yl + 2 * l + r);
+            t = __ldcg(B.cost_main + c);
+            h_resume = __ldcg(B.pert_cost + c);
+            left = nt - resume_ti;
+            tend = tl[resume_ti];
+            __syncwarp();              // every lane has its state before anyone may write that row
+        } else {
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if (gene_ok[r] && writer) Yc[2 * l + r] = y[r];
+        }
 
         // first derivative + starting step (Hairer/Norsett/Wanner II.4, max-norm)
         double f0[R], ys[R], f1[R];
@@ -233,6 +288,7 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
         const double dm = fmax(d1, d2);
         const double h1 = (dm <= 1e-15) ? fmax(1e-6, h0 * 1e-3) : pow(0.01 / dm, 1.0 / (M + 1));
         double h = fmin(100.0 * h0, h1);
+        if (B.resume) h = h_resume;    // the explicit pair's last proposal: the controller adapts
         // no previous step yet: with every stage's derivative = f(y0) the continued
         // "polynomial" is the Euler line y0 + c_i h f(y0)
         double hp = h, inv_hp = 1.0 / h;
@@ -246,6 +302,8 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
             double hs = h;
             bool hit = false;
             if (t + 1.01 * hs >= tend) { hs = tend - t; hit = true; }
+            const double hs_full = hs;
+            if (DUAL && role == 1) hs = hs_full * kPirkShadowRatio;
             double ha[S];
 #pragma unroll
             for (int j = 0; j < S; ++j) ha[j] = hs * arow[j];
@@ -331,13 +389,49 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
                 }
             }
             // non-negative floats order like their bit patterns
-            const float qf = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(ef)));
+            float qf = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(ef)));
 
             const float qc = fminf(fmaxf(qf, 1e-30f), 3.0e38f);
             float lg, ex;
             asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(qc));
             asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(ex) : "f"(kExpo * lg));
-            const float fac0 = 0.9f * ex;
+            float fac0 = 0.9f * ex;
+            bool fallback = false;         // the shorter attempt is the one that counts
+            if constexpr (DUAL) {
+                // both warps publish their outcome, one barrier, then both make the same choice
+                double *mine_slot = xch + (par * 2 + role) * SLOT;
+                const double *other_slot = xch + (par * 2 + (role ^ 1)) * SLOT;
+#pragma unroll
+                for (int j = 0; j < S; ++j)
+                    *reinterpret_cast<double2 *>(mine_slot + (j * 32 + lane) * 2) =
+                        make_double2(Fall[j][0], Fall[j][1]);
+                *reinterpret_cast<double2 *>(mine_slot + (S * 32 + lane) * 2) =
+                    make_double2(yn[0], yn[1]);
+                if (lane == 0)
+                    *reinterpret_cast<float2 *>(mine_slot + SLOT - 2) = make_float2(qf, fac0);
+                pair_barrier();
+                const float2 oq = *reinterpret_cast<const float2 *>(other_slot + SLOT - 2);
+                const float q_full = (role == 0) ? qf : oq.x, q_short = (role == 0) ? oq.x : qf;
+                const float f_full = (role == 0) ? fac0 : oq.y, f_short = (role == 0) ? oq.y : fac0;
+                fallback = !(q_full <= 1.0f);
+                const bool mine = fallback ? (role == 1) : (role == 0);
+                if (!mine && (fallback ? q_short : q_full) <= 1.0f) {
+#pragma unroll
+                    for (int j = 0; j < S; ++j) {
+                        const double2 v =
+                            *reinterpret_cast<const double2 *>(other_slot + (j * 32 + lane) * 2);
+                        Fall[j][0] = v.x; Fall[j][1] = v.y;
+                    }
+                    const double2 v =
+                        *reinterpret_cast<const double2 *>(other_slot + (S * 32 + lane) * 2);
+                    yn[0] = v.x; yn[1] = v.y;
+                }
+                qf = fallback ? q_short : q_full;
+                fac0 = fallback ? f_short : f_full;
+                hs = fallback ? hs_full * kPirkShadowRatio : hs_full;
+                if (fallback) hit = false;
+                par ^= 1;
+            }
             const bool accept = qf <= 1.0f;
             ++natt;
             bool failed = false;
@@ -352,8 +446,8 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
                     inv_hp = fast_rcp(hs);
                 }
                 float fac = fminf(kPirkFacMax, fmaxf(0.2f, fac0));
-                if (rejected) fac = fminf(fac, 1.0f);
-                rejected = false;
+                if (rejected || fallback) fac = fminf(fac, 1.0f);
+                rejected = fallback;       // the proposed step did fail: no growth next time
                 const double hnew = hs * (double)fac;
                 h = hit ? fmax(hnew, h) : hnew;
                 if (hit) {
@@ -403,16 +497,17 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
             }
         }
         part = warp_sum(part);
-        if (lane == 0) {
+        if (lane == 0 && role == 0) {
             B.cost_main[c] = part;
-            B.traj_steps[(size_t)c * P.K] = natt;
+            B.traj_steps[(size_t)c * P.K] = natt + (B.resume ? B.traj_steps[(size_t)c * P.K] : 0u);
             atomicAdd(&B.counters[(size_t)c * 3 + 0], (unsigned long long)nacc);
             atomicAdd(&B.counters[(size_t)c * 3 + 1], (unsigned long long)nrej);
             atomicAdd(&B.counters[(size_t)c * 3 + 2],
-                      (unsigned long long)((M + 1) * S) * natt + 2ull);
+                      (unsigned long long)((M + 1) * S * (DUAL ? 2 : 1)) * natt + 2ull);
             if (st) atomicOr(&B.status[c], st);
+            if (B.sp_attempts != nullptr) atomicAdd(B.sp_attempts, (unsigned long long)natt);
         }
-        if (B.mode == 0) {
+        if (B.mode == 0 && role == 0) {
             __threadfence();
             __syncwarp();
             unsigned old = 0;

@@ -12,7 +12,7 @@ eng.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"], p["pert"]
 for N in (64, 256, 512, 1024, 2048, 4096, 8192):
     X = uniform_population(p["lb"], p["ub"], N, seed=0)
     line = f"N={N:5d}"
-    for mode in ("off", "on", "stages"):
+    for mode in ("off", "on", "stages", "stages2", "handover"):
         eng.set_speculation(mode)
         eng.eval(X)
         ms = []
