@@ -361,11 +361,11 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak,
                          "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of the evaluation's two
-                         # kernels, one ncu --set full capture (profiles/r1_i_ncu_full_summary.txt);
+                         # dram__bytes_read.sum + dram__bytes_write.sum of the evaluation's three
+                         # kernels, one ncu --set full capture (profiles/r1_l_ncu_full_summary.txt);
                          # algorithmic bytes are X in + cost out = 0.72 MB: the path is compute-bound
-                         "traffic": 816640 + 853248,
-                         "traffic_source": "profiles/r1_i_ncu_full_summary.txt (bytes per evaluation)",
+                         "traffic": 846336 + 514048 + 901376,
+                         "traffic_source": "profiles/r1_l_ncu_full_summary.txt (bytes per evaluation)",
                          "kernel": eng.kernel_name, "kernel_ms": k_ms,
                          "time_series_kernel": eng.series_kernel_name(POP),
                          "step_attempts_per_launch": float(np.mean(attempts)),
