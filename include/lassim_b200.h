@@ -105,10 +105,12 @@ int lassim_set_method(lassim_handle *h, int method);
  *      instead of 12, same tolerances, weights and norm; steps are also limited so
  *      that no logistic term swings by more than 0.5 inside one (csrc/pirk_kernel.cuh)
  *   4  the same with a second warp attempting 0.7 of every step (as in 1)
+ *   6  the same with three warps attempting 1.15, 1 and 0.7 of the proposed step
+ *      (the largest that passes its error test is taken)
  *   5  hand-over: every time series starts in the standard kernel; those still
  *      going after a cap of attempts (three per four candidates of the batch, within
  *      [500, 8000]; LASSIM_SERIES_CAP in the environment overrides) stop at the
- *      step they are on and continue in kernel 4, launched behind it on the same
+ *      step they are on and continue in kernel 6, launched behind it on the same
  *      stream.  The many short time series stay cheap, the few long ones get the
  *      fast kernel almost to themselves
  *   2  automatic (default): 5 for batches of at most 16,384 candidates, else 0
@@ -279,8 +281,8 @@ const char *lassim_kernel_name(lassim_handle *h);
  * when the standard kernel does; twice the flops for speculative attempts (both
  * halves of the warp work); for the stage-parallel Gauss pair with S stages and
  * S corrections, (S+1)*S right-hand sides of 2*nnz + 5*n flops plus the stage
- * sums, predictor and estimate: 60*nnz + 474*n for S = 5, twice that when two
- * warps work (modes 4 and 5).  (No reference
+ * sums, predictor and estimate: 60*nnz + 474*n for S = 5, times the warps that
+ * work on a trajectory (2 in mode 4, 3 in modes 5 and 6).  (No reference
  * counterpart.) */
 long long lassim_series_flops_per_attempt(const lassim_handle *h, int N);
 const char *lassim_series_kernel_name(lassim_handle *h, int N);

@@ -201,11 +201,12 @@ class Engine:
     def set_speculation(self, mode="auto"):
         """Kernel for the time-series trajectories: 'off' (the standard one), 'on'
         (speculative half-warp attempts), 'stages' (stage-parallel Gauss pair, one warp
-        per trajectory), 'stages2' (the same with a second warp attempting a shorter step),
-        'handover' (standard kernel first, long time series continue in 'stages2') or 'auto'
+        per trajectory), 'stages2' / 'stages3' (the same with two / three warps attempting
+        different step sizes), 'handover' (standard kernel first, long time series continue
+        in 'stages3') or 'auto'
         ('handover' up to 16,384 candidates, 'off' beyond)."""
-        code = {"off": 0, "on": 1, "auto": 2, "stages": 3, "stages2": 4, "handover": 5,
-                0: 0, 1: 1, 2: 2, 3: 3, 4: 4, 5: 5, False: 0, True: 1}.get(mode)
+        code = {"off": 0, "on": 1, "auto": 2, "stages": 3, "stages2": 4, "handover": 5, "stages3": 6,
+                0: 0, 1: 1, 2: 2, 3: 3, 4: 4, 5: 5, 6: 6, False: 0, True: 1}.get(mode)
         if code is None:
             raise ValueError("time-series kernel mode %r (use 'off', 'on', 'stages' or 'auto')"
                              % (mode,))

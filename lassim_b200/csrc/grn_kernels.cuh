@@ -424,7 +424,10 @@ struct Grp {
 // small batches only.  Results do not depend on scheduling.
 constexpr double kShadowRatio = 0.7;
 
-template <int L, int R, class WT, int METHOD, bool FAST, bool PERIPH = false, bool SHADOW = false>
+// HANDOVER: the instantiation that serves the time series of a hand-over evaluation (it
+// checks the attempt cap after every attempt; the others carry no trace of it).
+template <int L, int R, class WT, int METHOD, bool FAST, bool PERIPH = false, bool SHADOW = false,
+          bool HANDOVER = false>
 __global__ void __launch_bounds__(threads_for(L), min_blocks_for(L))
 grn_cost_kernel(const DevProblem P, const DevBatch B) {
     static_assert(!SHADOW || (L == 16 && R == 1 && !PERIPH), "SHADOW: 16 lanes x 1 gene only");
@@ -726,7 +729,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
 
         // a time series over its attempt cap is handed to the kernel behind this one
         bool handover = false;
-        if constexpr (!PERIPH && !SHADOW)
+        if constexpr (HANDOVER)
             handover = active && k == 0 && B.series_cap != 0u && ti < nt && st == 0 &&
                        nacc + nrej >= B.series_cap;
         if (active && (ti >= nt || handover)) {

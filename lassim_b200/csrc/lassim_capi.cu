@@ -44,6 +44,7 @@ struct lassim_handle {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr;
     int speculate = 2;        // lassim_set_speculation mode (2 = automatic)
     unsigned series_cap = 0;      // hand-over cap; 0 = automatic (series_cap_for)
+    int handover_warps = 3;       // warps per trajectory of the kernel long time series move to
     bool timed = false;
     std::string err, kernel_name, series_kernel_name;
     long long launches = 0;
@@ -174,6 +175,9 @@ struct KernelChoice {
     size_t pirk_smem = 0;
     kernel_fn fn_pirk2 = nullptr;    // the same with a second warp attempting a shorter step
     size_t pirk2_smem = 0;
+    kernel_fn fn_pirk3 = nullptr;    // three warps, three step sizes
+    size_t pirk3_smem = 0;
+    kernel_fn fn_capped = nullptr;   // fn with the hand-over cap compiled in
 };
 
 // dynamic shared memory of one CTA: header (2^(j/256) table, reduction scratch)
@@ -190,6 +194,14 @@ kernel_fn dense_kernel(int method, bool fast) {
     return grn_cost_kernel<L, 1, DenseW<1, NC>, kMethodDP45, true>;
 }
 
+// the standard kernel with the attempt cap compiled in (time series of a hand-over evaluation)
+template <int NC>
+kernel_fn handover_kernel(int method) {
+    if (method == kMethodDOP853)
+        return grn_cost_kernel<16, 1, DenseW<1, NC>, kMethodDOP853, true, false, false, true>;
+    return grn_cost_kernel<16, 1, DenseW<1, NC>, kMethodDP45, true, false, false, true>;
+}
+
 template <int NC>
 kernel_fn shadow_kernel(int method) {
     if (method == kMethodDOP853)
@@ -200,15 +212,19 @@ kernel_fn shadow_kernel(int method) {
 // stage-parallel time-series kernel: 5 Gauss stages x 6 lanes for n <= 12, 4 x 8 up to 16
 void pirk_kernel(int n, KernelChoice *out) {
     if (n <= 12) {
-        out->fn_pirk = grn_series_pirk_kernel<5, 6, 12, true>;
-        out->pirk_smem = pirk_smem_doubles(5, 6, 12, false) * sizeof(double);
-        out->fn_pirk2 = grn_series_pirk_kernel<5, 6, 12, true, true>;
-        out->pirk2_smem = pirk_smem_doubles(5, 6, 12, true) * sizeof(double);
+        out->fn_pirk = grn_series_pirk_kernel<5, 6, 12, true, 1>;
+        out->pirk_smem = pirk_smem_doubles(5, 6, 12, 1) * sizeof(double);
+        out->fn_pirk2 = grn_series_pirk_kernel<5, 6, 12, true, 2>;
+        out->pirk2_smem = pirk_smem_doubles(5, 6, 12, 2) * sizeof(double);
+        out->fn_pirk3 = grn_series_pirk_kernel<5, 6, 12, true, 3>;
+        out->pirk3_smem = pirk_smem_doubles(5, 6, 12, 3) * sizeof(double);
     } else {
-        out->fn_pirk = grn_series_pirk_kernel<4, 8, 16, true>;
-        out->pirk_smem = pirk_smem_doubles(4, 8, 16, false) * sizeof(double);
-        out->fn_pirk2 = grn_series_pirk_kernel<4, 8, 16, true, true>;
-        out->pirk2_smem = pirk_smem_doubles(4, 8, 16, true) * sizeof(double);
+        out->fn_pirk = grn_series_pirk_kernel<4, 8, 16, true, 1>;
+        out->pirk_smem = pirk_smem_doubles(4, 8, 16, 1) * sizeof(double);
+        out->fn_pirk2 = grn_series_pirk_kernel<4, 8, 16, true, 2>;
+        out->pirk2_smem = pirk_smem_doubles(4, 8, 16, 2) * sizeof(double);
+        out->fn_pirk3 = grn_series_pirk_kernel<4, 8, 16, true, 3>;
+        out->pirk3_smem = pirk_smem_doubles(4, 8, 16, 3) * sizeof(double);
     }
 }
 
@@ -254,6 +270,10 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
                            : nc <= 12 ? shadow_kernel<12>(method)
                                       : shadow_kernel<16>(method);
             pirk_kernel(n, out);
+            out->fn_capped = nc <= 4 ? handover_kernel<4>(method)
+                           : nc <= 8 ? handover_kernel<8>(method)
+                           : nc <= 12 ? handover_kernel<12>(method)
+                                      : handover_kernel<16>(method);
         }
         return true;
     }
@@ -294,6 +314,7 @@ int series_mode(const lassim_handle *h, const KernelChoice &kc, int N, bool peri
     if (periph) return 0;
     const bool automatic = h->speculate == 2;
     if (kc.fn_pirk2 != nullptr && (h->speculate == 5 || (automatic && N <= 16384))) return 5;
+    if (kc.fn_pirk3 != nullptr && h->speculate == 6) return 6;
     if (kc.fn_pirk2 != nullptr && h->speculate == 4) return 4;
     if (kc.fn_pirk != nullptr && h->speculate == 3) return 3;
     if (kc.fn_shadow != nullptr && h->speculate == 1) return 1;
@@ -317,7 +338,7 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
     // time-series kernel of a small batch: 3 = stage-parallel, 1 = speculative, 2 = auto
     // (stage-parallel where built, for batches of at most 2048 candidates)
     const int smode = series_mode(h, kc, N, periph);
-    const kernel_fn series_fn = smode >= 4 ? kc.fn_pirk2 : smode == 3 ? kc.fn_pirk
+    const kernel_fn series_fn = smode == 6 ? kc.fn_pirk3 : smode >= 4 ? kc.fn_pirk2 : smode == 3 ? kc.fn_pirk
                               : smode == 1 ? kc.fn_shadow : nullptr;
     const bool speculate = series_fn != nullptr;
     auto launch = [&](kernel_fn fn, int threads, size_t smem, int lanes_per_item, unsigned begin,
@@ -356,13 +377,19 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
         if (smode == 5) {
             // every time series starts in the standard kernel; the ones still going after
             // series_cap attempts continue in the two-warp stage-parallel kernel behind it
-            CU(launch(kc.fn, threads, smem, kc.L, 0u, (unsigned)N, counters, s, series_cap_for(h, N), 0));
-            CU(launch(kc.fn_pirk2, kPirkThreads, kc.pirk2_smem, 64, 0u, (unsigned)N, counters + 3, s,
-                      0u, 1));
-        } else if (smode == 4)
-            CU(launch(series_fn, kPirkThreads, kc.pirk2_smem, 64, 0u, (unsigned)N, counters, s));
+            CU(launch(kc.fn_capped, threads, smem, kc.L, 0u, (unsigned)N, counters, s, series_cap_for(h, N), 0));
+            if (h->handover_warps == 3)
+                CU(launch(kc.fn_pirk3, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters + 3,
+                          s, 0u, 1));
+            else
+                CU(launch(kc.fn_pirk2, pirk_threads(2), kc.pirk2_smem, 64, 0u, (unsigned)N, counters + 3,
+                          s, 0u, 1));
+        } else if (smode == 6)
+            CU(launch(series_fn, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters, s));
+        else if (smode == 4)
+            CU(launch(series_fn, pirk_threads(2), kc.pirk2_smem, 64, 0u, (unsigned)N, counters, s));
         else if (smode == 3)
-            CU(launch(series_fn, kPirkThreads, kc.pirk_smem, 32, 0u, (unsigned)N, counters, s));
+            CU(launch(series_fn, pirk_threads(1), kc.pirk_smem, 32, 0u, (unsigned)N, counters, s));
         else
             CU(launch(series_fn, threads, smem, 32, 0u, (unsigned)N, counters, s));
         if (rest > 0) {
@@ -518,6 +545,7 @@ int lassim_create(int device, lassim_handle **out) {
     }
     if (const char *sp = getenv("LASSIM_SPECULATE")) h->speculate = atoi(sp);
     if (const char *sp = getenv("LASSIM_SERIES_CAP")) h->series_cap = (unsigned)atoi(sp);
+    if (const char *sp = getenv("LASSIM_HANDOVER_WARPS")) h->handover_warps = atoi(sp) == 3 ? 3 : 2;
     double tab[kExpTable];
     for (int j = 0; j < kExpTable; ++j) tab[j] = exp2((double)j / (double)kExpTable);
     if (cudaMemcpyToSymbol(c_exp2_table, tab, sizeof(tab)) != cudaSuccess) {
@@ -657,7 +685,7 @@ int lassim_set_series_cap(lassim_handle *h, unsigned int attempts) {
 
 int lassim_set_speculation(lassim_handle *h, int mode) {
     if (!h) return LASSIM_E_INVALID;
-    if (mode < 0 || mode > 5)
+    if (mode < 0 || mode > 6)
         return fail(h, LASSIM_E_INVALID,
                     "time-series kernel mode %d (0 standard, 1 speculative, 2 auto, 3 stage-parallel, "
                     "4 stage-parallel + speculative)", mode);
@@ -691,13 +719,16 @@ long long lassim_series_flops_per_attempt(const lassim_handle *h, int N) {
     switch (smode) {
         case 3:
         case 4:
-        case 5: {
+        case 5:
+        case 6: {
             // S stages, M = S corrections: (M+1)*S RHS evaluations of 2*nnz + 5*n flops,
             // M*S stage sums and the predictor (2*S flops per gene each), two weighted
             // sums for solution and estimate (2*S each), 4 for the error measure
             const long long S = h->n <= 12 ? 5 : 4, M = S;
             const long long one = (M + 1) * S * (2 * nnz + 5 * n) + (M * S + S + 2) * 2 * S * n + 4 * n;
-            return smode >= 4 ? 2 * one : one;      // 4, 5: both warps of the pair work
+            // every warp of a trajectory's group works
+            const long long warps = smode == 6 ? 3 : smode == 5 ? h->handover_warps : smode == 4 ? 2 : 1;
+            return warps * one;
         }
         case 1: return 2 * lassim_flops_per_attempt(h);     // both halves of the warp
         default: return lassim_flops_per_attempt(h);
@@ -723,11 +754,14 @@ const char *lassim_series_kernel_name(lassim_handle *h, int N) {
         case 3:
         case 4:
         case 5:
+        case 6: {
+            const int warps = smode == 6 ? 3 : smode == 5 ? h->handover_warps : smode == 4 ? 2 : 1;
             h->series_kernel_name = std::string(h->n <= 12 ? "grn_series_pirk_kernel<5 Gauss stages x 6 lanes"
                                                             : "grn_series_pirk_kernel<4 Gauss stages x 8 lanes") +
-                                    (smode >= 4 ? ", two step sizes>" : ">") +
+                                    (warps == 3 ? ", three step sizes>" : warps == 2 ? ", two step sizes>" : ">") +
                                     (smode == 5 ? " behind " + std::string(lassim_kernel_name(h)) : "");
             break;
+        }
         case 1:
             h->series_kernel_name = std::string("grn_cost_kernel<") + kc.name + ", speculative, " +
                                     (h->method == kMethodDOP853 ? "dop853>" : "dp45>");

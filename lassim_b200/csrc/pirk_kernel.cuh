@@ -52,7 +52,8 @@ namespace lassim {
 #endif
 constexpr float kPirkFacMax = LASSIM_PIRK_FACMAX;
 constexpr float kPirkSwing = LASSIM_PIRK_SWING;
-constexpr int kPirkThreads = 128;
+// threads per CTA: 4 trajectories of one warp, 2 of two warps, 2 of three warps
+__host__ __device__ constexpr int pirk_threads(int WARPS) { return WARPS == 3 ? 192 : 128; }
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
@@ -74,28 +75,35 @@ __host__ __device__ constexpr int pirk_lines(int LPS) { return (32 + LPS - 1) / 
 __host__ __device__ constexpr int pirk_stride(int LPS, int NC) {
     return (LPS % 8 == 0) ? NC + 2 : 2 * LPS;
 }
-// DUAL: doubles of one exchange slot of a warp pair (solution + derivatives of every lane,
-// error measure and step factor), S stages
+// WARPS > 1: doubles of one exchange slot of a warp group (solution + derivatives of every
+// lane, error measure and step factor), S stages
 __host__ __device__ constexpr int pirk_slot(int S) { return 32 * 2 * (S + 1) + 2; }
 // per warp: derivative lines, state lines, logistic values (float2 per lane);
-// DUAL adds, per pair of warps, 2 (parity) x 2 (role) exchange slots and a work-item slot
-constexpr size_t pirk_smem_doubles(int S, int LPS, int NC, bool dual) {
+// WARPS > 1 adds, per group of warps, 2 (parity) x WARPS (role) exchange slots and a
+// work-item slot
+constexpr size_t pirk_smem_doubles(int S, int LPS, int NC, int warps) {
     return (size_t)kSmemHeader +
-           (size_t)(kPirkThreads / 32) *
+           (size_t)(pirk_threads(warps) / 32) *
                (2 * pirk_lines(LPS) * pirk_stride(LPS, NC) + pirk_lines(LPS) * LPS) +
-           (dual ? (size_t)(kPirkThreads / 64) * (4 * pirk_slot(S) + 2) : 0);
+           (warps > 1 ? (size_t)(pirk_threads(warps) / (32 * warps)) *
+                            (2 * warps * pirk_slot(S) + 2) : 0);
 }
 
-// Step ratio of the second warp of a pair (DUAL), as in the speculative explicit kernel.
-constexpr double kPirkShadowRatio = 0.7;
+// Step sizes attempted side by side, as multiples of the controller's proposal, largest
+// first: two warps {1, 0.7} (as in the speculative explicit kernel), three {1.15, 1, 0.7}.
+__host__ __device__ constexpr double pirk_ratio(int WARPS, int role) {
+    return WARPS == 2 ? (role == 0 ? 1.0 : 0.7)
+         : WARPS == 3 ? (role == 0 ? 1.15 : role == 1 ? 1.0 : 0.7)
+                      : 1.0;
+}
 
-// DUAL: two warps per trajectory.  Both carry the same state; warp 0 of the pair attempts
-// the proposed step, warp 1 the same step from the same state at 0.7 of the size, and when
-// the full step fails its test while the shorter one passes, the shorter one is taken instead
-// of starting over (a limit cycle rejects 17-25 % of its attempts).  One exchange through
-// shared memory and one named barrier per attempt; the warps sit on different schedulers.
-template <int S, int LPS, int NC, bool FAST, bool DUAL = false>
-__global__ void __launch_bounds__(kPirkThreads, 2)
+// WARPS > 1: that many warps per trajectory, on different schedulers.  All carry the same
+// state; each attempts the step from that state at its own multiple of the proposed size; the
+// largest attempt that passes its error test is taken by all of them (a limit cycle rejects
+// 17-25 % of its proposed steps, and a step 15 % above the proposal passes more often than
+// not).  One exchange through shared memory and one named barrier per attempt.
+template <int S, int LPS, int NC, bool FAST, int WARPS = 1>
+__global__ void __launch_bounds__(pirk_threads(WARPS), WARPS == 3 ? 1 : 2)
 grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
     static_assert(S * LPS <= 32 && 2 * LPS <= NC + 3, "stages x lanes must fit one warp");
     static_assert(S == 4 || S == 5, "predictor polynomial written out for 4 and 5 stages");
@@ -117,16 +125,18 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
     double *fline = smem + kSmemHeader + wid * PER_WARP;
     double *yline = fline + LINES * STR;
     float2 *sline = reinterpret_cast<float2 *>(yline + LINES * STR);
-    // warp pair (DUAL): role 0 attempts the proposed step, role 1 the shorter one
-    const int pairq = wid >> 1, role = DUAL ? (wid & 1) : 0;
+    // warp group (WARPS > 1): role r attempts pirk_ratio(WARPS, r) times the proposed step
+    constexpr bool DUAL = WARPS > 1;
+    constexpr int THREADS = pirk_threads(WARPS);
+    const int pairq = wid / WARPS, role = wid - pairq * WARPS;
     constexpr int SLOT = pirk_slot(S);
-    double *xch = smem + kSmemHeader + (kPirkThreads / 32) * PER_WARP + pairq * (4 * SLOT + 2);
-    unsigned *work_slot = reinterpret_cast<unsigned *>(xch + 4 * SLOT);
+    double *xch = smem + kSmemHeader + (THREADS / 32) * PER_WARP + pairq * (2 * WARPS * SLOT + 2);
+    unsigned *work_slot = reinterpret_cast<unsigned *>(xch + 2 * WARPS * SLOT);
     int par = 0;
     auto pair_barrier = [&]() {
         if constexpr (DUAL) {          // literal ids: the kernel reserves 3 barriers, not all 16
-            if (pairq == 0) asm volatile("bar.sync 1, 64;" ::: "memory");
-            else asm volatile("bar.sync 2, 64;" ::: "memory");
+            if (pairq == 0) asm volatile("bar.sync 1, %0;" ::"n"(32 * WARPS) : "memory");
+            else asm volatile("bar.sync 2, %0;" ::"n"(32 * WARPS) : "memory");
         }
     };
     fill_exp2_table(tab);
@@ -296,14 +306,26 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
         for (int j = 0; j < S; ++j) { Fp[j][0] = f0[0]; Fp[j][1] = f0[1]; }
         __syncwarp();
 
-        const unsigned budget = P.max_steps;
+        // attempts left in the budget, counted down in a register (comparing with the kernel
+        // parameter would reload it from the constant bank at the end of every attempt)
+        unsigned budget_left = P.max_steps;
+        asm volatile("" : "+r"(budget_left));
         while (left > 0) {
             // ------------------------------------------------ one attempt
-            double hs = h;
-            bool hit = false;
-            if (t + 1.01 * hs >= tend) { hs = tend - t; hit = true; }
-            const double hs_full = hs;
-            if (DUAL && role == 1) hs = hs_full * kPirkShadowRatio;
+            // every role's step (all warps know all of them), clipped to the next sample time
+            double hs_of[WARPS];
+            bool hit_of[WARPS];
+#pragma unroll
+            for (int q = 0; q < WARPS; ++q) {
+                hs_of[q] = h * pirk_ratio(WARPS, q);
+                hit_of[q] = false;
+                if (t + 1.01 * hs_of[q] >= tend) { hs_of[q] = tend - t; hit_of[q] = true; }
+            }
+            double hs = hs_of[0];
+            bool hit = hit_of[0];
+#pragma unroll
+            for (int q = 1; q < WARPS; ++q)
+                if (role == q) { hs = hs_of[q]; hit = hit_of[q]; }
             double ha[S];
 #pragma unroll
             for (int j = 0; j < S; ++j) ha[j] = hs * arow[j];
@@ -398,9 +420,9 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
             float fac0 = 0.9f * ex;
             bool fallback = false;         // the shorter attempt is the one that counts
             if constexpr (DUAL) {
-                // both warps publish their outcome, one barrier, then both make the same choice
-                double *mine_slot = xch + (par * 2 + role) * SLOT;
-                const double *other_slot = xch + (par * 2 + (role ^ 1)) * SLOT;
+                // every warp publishes its outcome, one barrier, then all make the same choice:
+                // the largest attempt that passed (roles are ordered by step size)
+                double *mine_slot = xch + (par * WARPS + role) * SLOT;
 #pragma unroll
                 for (int j = 0; j < S; ++j)
                     *reinterpret_cast<double2 *>(mine_slot + (j * 32 + lane) * 2) =
@@ -410,26 +432,31 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
                 if (lane == 0)
                     *reinterpret_cast<float2 *>(mine_slot + SLOT - 2) = make_float2(qf, fac0);
                 pair_barrier();
-                const float2 oq = *reinterpret_cast<const float2 *>(other_slot + SLOT - 2);
-                const float q_full = (role == 0) ? qf : oq.x, q_short = (role == 0) ? oq.x : qf;
-                const float f_full = (role == 0) ? fac0 : oq.y, f_short = (role == 0) ? oq.y : fac0;
-                fallback = !(q_full <= 1.0f);
-                const bool mine = fallback ? (role == 1) : (role == 0);
-                if (!mine && (fallback ? q_short : q_full) <= 1.0f) {
+                int pick = WARPS - 1;          // nobody passed: the smallest attempt sets the next size
+                float2 qo[WARPS];
+#pragma unroll
+                for (int q = WARPS - 1; q >= 0; --q) {
+                    qo[q] = *reinterpret_cast<const float2 *>(xch + (par * WARPS + q) * SLOT + SLOT - 2);
+                    if (qo[q].x <= 1.0f) pick = q;
+                }
+                float2 chosen = qo[0];
+                hs = hs_of[0]; hit = hit_of[0];
+#pragma unroll
+                for (int q = 1; q < WARPS; ++q)
+                    if (pick == q) { chosen = qo[q]; hs = hs_of[q]; hit = hit_of[q]; }
+                if (pick != role && chosen.x <= 1.0f) {
+                    const double *from = xch + (par * WARPS + pick) * SLOT;
 #pragma unroll
                     for (int j = 0; j < S; ++j) {
-                        const double2 v =
-                            *reinterpret_cast<const double2 *>(other_slot + (j * 32 + lane) * 2);
+                        const double2 v = *reinterpret_cast<const double2 *>(from + (j * 32 + lane) * 2);
                         Fall[j][0] = v.x; Fall[j][1] = v.y;
                     }
-                    const double2 v =
-                        *reinterpret_cast<const double2 *>(other_slot + (S * 32 + lane) * 2);
+                    const double2 v = *reinterpret_cast<const double2 *>(from + (S * 32 + lane) * 2);
                     yn[0] = v.x; yn[1] = v.y;
                 }
-                qf = fallback ? q_short : q_full;
-                fac0 = fallback ? f_short : f_full;
-                hs = fallback ? hs_full * kPirkShadowRatio : hs_full;
-                if (fallback) hit = false;
+                qf = chosen.x;
+                fac0 = chosen.y;
+                fallback = pick > 0;           // a larger attempt failed: no growth next time
                 par ^= 1;
             }
             const bool accept = qf <= 1.0f;
@@ -464,7 +491,8 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
                 h = hs * (double)fmaxf(0.2f, fminf(fac0, 1.0f));
                 if (!(fabs(h) > 1e-290) || t + h == t) { st |= 2; failed = true; }
             }
-            if (!failed && left > 0 && natt >= budget) { st |= 1; failed = true; }
+            --budget_left;
+            if (!failed && left > 0 && budget_left == 0u) { st |= 1; failed = true; }
             if (failed) {
                 for (int s = nt - left; s < nt; ++s)
 #pragma unroll
@@ -503,7 +531,7 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
             atomicAdd(&B.counters[(size_t)c * 3 + 0], (unsigned long long)nacc);
             atomicAdd(&B.counters[(size_t)c * 3 + 1], (unsigned long long)nrej);
             atomicAdd(&B.counters[(size_t)c * 3 + 2],
-                      (unsigned long long)((M + 1) * S * (DUAL ? 2 : 1)) * natt + 2ull);
+                      (unsigned long long)((M + 1) * S * WARPS) * natt + 2ull);
             if (st) atomicOr(&B.status[c], st);
             if (B.sp_attempts != nullptr) atomicAdd(B.sp_attempts, (unsigned long long)natt);
         }

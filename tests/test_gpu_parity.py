@@ -492,8 +492,9 @@ def test_argument_errors(engine, th2):
 def test_time_series_kernels_stay_inside_the_error_control(engine, th2, name):
     """Small batches integrate their time series with one warp per trajectory
     (lassim_set_speculation): 'stages' = the stage-parallel Gauss pair, 'stages2' =
-    the same with a second warp attempting 0.7 of every step, 'handover' = standard
-    kernel first, time series over the attempt cap continue in 'stages2' (what
+    the same with a second warp attempting 0.7 of every step, 'stages3' = three warps
+    attempting 1.15, 1 and 0.7 of it, 'handover' = standard kernel first, time series
+    over the attempt cap continue in 'stages3' (what
     'auto' picks up to 16,384 candidates), 'on' = the explicit pair with a second,
     shorter attempt in the other half of the warp, 'off' = the standard kernel.  All must pass the parity
     gate, differ from each other only at the level of the integration tolerance,
@@ -503,7 +504,7 @@ def test_time_series_kernels_stay_inside_the_error_control(engine, th2, name):
     bind_th2(engine, th2)
     well = rel(g["ref_cost_main"], g["tight_cost_main"]) <= 1e-7
     res = {}
-    for mode in ("off", "on", "stages", "stages2", "handover", "auto"):
+    for mode in ("off", "on", "stages", "stages2", "stages3", "handover", "auto"):
         engine.set_speculation(mode)
         a = engine.eval(g["X"], details=True)
         b = engine.eval(g["X"], details=True)
@@ -517,14 +518,14 @@ def test_time_series_kernels_stay_inside_the_error_control(engine, th2, name):
         assert err[well].max() <= TRAJ_RTOL
         res[mode] = a
     np.testing.assert_array_equal(res["handover"]["cost"], res["auto"]["cost"])     # N <= 16384
-    for mode in ("on", "stages", "stages2", "handover"):
+    for mode in ("on", "stages", "stages2", "stages3", "handover"):
         assert rel(res[mode]["cost_main"], res["off"]["cost_main"])[well].max() <= COST_RTOL
         # the knock-down trajectories run on the standard kernel either way
         np.testing.assert_array_equal(res[mode]["pert_cost"], res["off"]["pert_cost"])
     # fewer sequential attempts on the time series with speculation; the Gauss pair
     # reports its own attempts (6 right-hand sides each instead of 12)
     steps = {}
-    for mode in ("off", "on", "stages", "stages2"):
+    for mode in ("off", "on", "stages", "stages2", "stages3"):
         engine.set_speculation(mode)
         engine.eval(g["X"])
         steps[mode] = engine.last_traj_steps(N)[:, 0]
@@ -532,6 +533,7 @@ def test_time_series_kernels_stay_inside_the_error_control(engine, th2, name):
     assert (steps["stages"] > 0).all()
     assert steps["stages2"].max() < steps["stages"].max()
     assert steps["stages2"].sum() < steps["stages"].sum()
+    assert steps["stages3"].sum() < steps["stages2"].sum()
     # hand-over: short time series never leave the standard kernel (same attempts as 'off'),
     # the ones over the cap continue in the stage-parallel kernel
     cap = int(np.median(steps["off"]))
@@ -558,7 +560,7 @@ def test_stage_parallel_kernel_resolves_a_switch_inside_a_step(engine, th2, th2_
     converges on a smooth curve through a near-jump).  The logistic-swing limit of
     the stage-parallel kernel has to catch it: without it this row is off by 9e-6."""
     bind_th2(engine, th2, pert=False)
-    for mode in ("stages", "stages2", "handover"):
+    for mode in ("stages", "stages2", "stages3", "handover"):
         engine.set_speculation(mode)
         out = engine.eval(th2_late["X"][52:54], details=True)
         assert (out["status"] == 0).all()

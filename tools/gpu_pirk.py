@@ -12,7 +12,7 @@ from workloads import uniform_population
 G = os.path.join(REPO, "tests", "golden")
 p = dict(np.load(os.path.join(G, "th2_problem.npz")))
 eng = Engine(0)
-MODES = ("off", "on", "stages", "stages2", "handover")
+MODES = ("off", "on", "stages", "stages2", "stages3", "handover")
 for name in ("th2_uniform", "th2_late"):
     g = np.load(os.path.join(G, name + ".npz"))
     eng.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"], p["pert"], float(g["pert_factor"]))
