@@ -105,13 +105,13 @@ int lassim_set_method(lassim_handle *h, int method);
  *      instead of 12, same tolerances, weights and norm; steps are also limited so
  *      that no logistic term swings by more than 0.5 inside one (csrc/pirk_kernel.cuh)
  *   4  the same with a second warp attempting 0.7 of every step (as in 1)
- *   6  the same with three warps attempting 1.15, 1 and 0.7 of the proposed step
+ *   6  the same with three warps attempting 1.2, 1 and 0.7 of the proposed step
  *      (the largest that passes its error test is taken)
  *   5  hand-over: every time series starts in the standard kernel; those still
  *      going after a cap of attempts (three per four candidates of the batch, within
  *      [500, 8000]; LASSIM_SERIES_CAP in the environment overrides) stop at the
- *      step they are on and continue in kernel 6, launched behind it on the same
- *      stream.  The many short time series stay cheap, the few long ones get the
+ *      step they are on and continue in kernel 6 (512 to 8192 candidates) or 4,
+ *      launched behind it on the same stream.  The many short time series stay cheap, the few long ones get the
  *      fast kernel almost to themselves
  *   2  automatic (default): 5 for batches of at most 16,384 candidates, else 0
  * Results are deterministic for a given mode and batch size and stay inside the
@@ -292,6 +292,12 @@ const char *lassim_series_kernel_name(lassim_handle *h, int N);
  * standard kernel; lassim_last_traj_steps reports the sum of both).  Blocks until
  * the evaluation has finished.  (No reference counterpart.) */
 int lassim_last_stage_parallel_attempts(lassim_handle *h, unsigned long long *attempts);
+
+/* Device time of the stage-parallel kernel of the last evaluation in milliseconds
+ * (CUDA events on the launching stream around that one launch); LASSIM_E_STATE if
+ * the last evaluation did not use it.  Blocks until it has finished.  (No reference
+ * counterpart.) */
+int lassim_last_stage_parallel_ms(lassim_handle *h, float *ms);
 
 /* Number of kernels this handle has launched so far (an evaluation is one launch,
  * or two concurrent ones when speculation is active). */

@@ -104,6 +104,8 @@ def load_library():
     lib.lassim_series_kernel_name.restype = ctypes.c_char_p
     lib.lassim_last_stage_parallel_attempts.argtypes = [H, c_ull_p]
     lib.lassim_last_stage_parallel_attempts.restype = ctypes.c_int
+    lib.lassim_last_stage_parallel_ms.argtypes = [H, ctypes.POINTER(ctypes.c_float)]
+    lib.lassim_last_stage_parallel_ms.restype = ctypes.c_int
     lib.lassim_launch_count.argtypes = [H]
     lib.lassim_launch_count.restype = ctypes.c_longlong
     lib.lassim_last_kernel_ms.argtypes = [H, ctypes.POINTER(ctypes.c_float)]
@@ -427,6 +429,13 @@ class Engine:
         self._check(self._lib.lassim_last_stage_parallel_attempts(self._h, ctypes.byref(v)),
                     "lassim_last_stage_parallel_attempts")
         return int(v.value)
+
+    def last_stage_parallel_ms(self):
+        """Device time of the stage-parallel kernel of the last evaluation (ms)."""
+        ms = ctypes.c_float()
+        self._check(self._lib.lassim_last_stage_parallel_ms(self._h, ctypes.byref(ms)),
+                    "lassim_last_stage_parallel_ms")
+        return float(ms.value)
 
     def series_kernel_name(self, N):
         return self._lib.lassim_series_kernel_name(self._h, int(N)).decode()

@@ -42,9 +42,11 @@ struct lassim_handle {
     int sm_count = 0;
     cudaStream_t stream = nullptr, stream2 = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_sp0 = nullptr, ev_sp1 = nullptr;   // around the stage-parallel kernel
+    bool sp_timed = false;
     int speculate = 2;        // lassim_set_speculation mode (2 = automatic)
     unsigned series_cap = 0;      // hand-over cap; 0 = automatic (series_cap_for)
-    int handover_warps = 3;       // warps per trajectory of the kernel long time series move to
+    int handover_warps = 0;       // warps per trajectory of the kernel long time series move to; 0 = by batch size
     bool timed = false;
     std::string err, kernel_name, series_kernel_name;
     long long launches = 0;
@@ -326,6 +328,15 @@ int series_mode(const lassim_handle *h, const KernelChoice &kc, int N, bool peri
 // few enough that the long ones lose little time at the slower pace.  Measured optimum
 // (table above; 1024 candidates: 300 -> 23.8 ms, 500 -> 22.9, 750 -> 22.5, 1000 -> 22.8,
 // 1500 -> 23.4, 3000 -> 26.4, medians): three attempts per four candidates, within [500, 8000].
+// Warps per handed-over trajectory.  Three step sizes pay where the batch waits for limit
+// cycles in a stage-parallel kernel that is not crowded (medians, ms, two / three warps, two
+// populations each: 64 candidates 14.8 / 16.8 and 11.7 / 13.4; 256: 16.9 / 17.8 and 15.3 / 14.6;
+// 1024: 22.6 / 21.7 and 28.7 / 27.2; 4096: 33.1 / 30.9; 16,384: 60.6 / 62.4).
+int handover_warps_for(const lassim_handle *h, int N) {
+    if (h->handover_warps == 2 || h->handover_warps == 3) return h->handover_warps;
+    return (N >= 512 && N <= 8192) ? 3 : 2;
+}
+
 unsigned series_cap_for(const lassim_handle *h, int N) {
     if (h->series_cap != 0u) return h->series_cap;
     const long long c = 3LL * N / 4;
@@ -368,6 +379,7 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
     const int threads = threads_for(kc.L);
     const size_t smem = smem_bytes(kc);
     const unsigned total = (unsigned)N * (unsigned)traj_per_candidate;
+    h->sp_timed = false;
     if (speculate) {
         const unsigned rest = total - (unsigned)N;
         if (rest > 0) {
@@ -378,20 +390,28 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
             // every time series starts in the standard kernel; the ones still going after
             // series_cap attempts continue in the two-warp stage-parallel kernel behind it
             CU(launch(kc.fn_capped, threads, smem, kc.L, 0u, (unsigned)N, counters, s, series_cap_for(h, N), 0));
-            if (h->handover_warps == 3)
+            CU(cudaEventRecord(h->ev_sp0, s));
+            if (handover_warps_for(h, N) == 3)
                 CU(launch(kc.fn_pirk3, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters + 3,
                           s, 0u, 1));
             else
                 CU(launch(kc.fn_pirk2, pirk_threads(2), kc.pirk2_smem, 64, 0u, (unsigned)N, counters + 3,
                           s, 0u, 1));
-        } else if (smode == 6)
-            CU(launch(series_fn, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters, s));
-        else if (smode == 4)
-            CU(launch(series_fn, pirk_threads(2), kc.pirk2_smem, 64, 0u, (unsigned)N, counters, s));
-        else if (smode == 3)
-            CU(launch(series_fn, pirk_threads(1), kc.pirk_smem, 32, 0u, (unsigned)N, counters, s));
-        else
+        } else if (smode == 1) {
             CU(launch(series_fn, threads, smem, 32, 0u, (unsigned)N, counters, s));
+        } else {
+            CU(cudaEventRecord(h->ev_sp0, s));
+            if (smode == 6)
+                CU(launch(series_fn, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters, s));
+            else if (smode == 4)
+                CU(launch(series_fn, pirk_threads(2), kc.pirk2_smem, 64, 0u, (unsigned)N, counters, s));
+            else
+                CU(launch(series_fn, pirk_threads(1), kc.pirk_smem, 32, 0u, (unsigned)N, counters, s));
+        }
+        if (smode != 1) {
+            CU(cudaEventRecord(h->ev_sp1, s));
+            h->sp_timed = true;
+        }
         if (rest > 0) {
             CU(launch(kc.fn, threads, smem, kc.L, (unsigned)N, rest, counters + 1, h->stream2));
             CU(cudaEventRecord(h->ev_join, h->stream2));
@@ -538,6 +558,7 @@ int lassim_create(int device, lassim_handle **out) {
     if (cudaStreamCreateWithPriority(&h->stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
         cudaStreamCreateWithPriority(&h->stream2, cudaStreamNonBlocking, prio_lo) != cudaSuccess ||
         cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess ||
+        cudaEventCreate(&h->ev_sp0) != cudaSuccess || cudaEventCreate(&h->ev_sp1) != cudaSuccess ||
         cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) != cudaSuccess) {
         delete h;
@@ -545,7 +566,7 @@ int lassim_create(int device, lassim_handle **out) {
     }
     if (const char *sp = getenv("LASSIM_SPECULATE")) h->speculate = atoi(sp);
     if (const char *sp = getenv("LASSIM_SERIES_CAP")) h->series_cap = (unsigned)atoi(sp);
-    if (const char *sp = getenv("LASSIM_HANDOVER_WARPS")) h->handover_warps = atoi(sp) == 3 ? 3 : 2;
+    if (const char *sp = getenv("LASSIM_HANDOVER_WARPS")) h->handover_warps = atoi(sp);
     double tab[kExpTable];
     for (int j = 0; j < kExpTable; ++j) tab[j] = exp2((double)j / (double)kExpTable);
     if (cudaMemcpyToSymbol(c_exp2_table, tab, sizeof(tab)) != cudaSuccess) {
@@ -574,6 +595,7 @@ int lassim_destroy(lassim_handle *h) {
     h->d_zero.release(); h->d_steps.release(); h->d_long.release();
     cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
     cudaEventDestroy(h->ev_fork); cudaEventDestroy(h->ev_join);
+    cudaEventDestroy(h->ev_sp0); cudaEventDestroy(h->ev_sp1);
     cudaStreamDestroy(h->stream2);
     cudaStreamDestroy(h->stream);
     delete h;
@@ -727,7 +749,7 @@ long long lassim_series_flops_per_attempt(const lassim_handle *h, int N) {
             const long long S = h->n <= 12 ? 5 : 4, M = S;
             const long long one = (M + 1) * S * (2 * nnz + 5 * n) + (M * S + S + 2) * 2 * S * n + 4 * n;
             // every warp of a trajectory's group works
-            const long long warps = smode == 6 ? 3 : smode == 5 ? h->handover_warps : smode == 4 ? 2 : 1;
+            const long long warps = smode == 6 ? 3 : smode == 5 ? handover_warps_for(h, N) : smode == 4 ? 2 : 1;
             return warps * one;
         }
         case 1: return 2 * lassim_flops_per_attempt(h);     // both halves of the warp
@@ -755,7 +777,7 @@ const char *lassim_series_kernel_name(lassim_handle *h, int N) {
         case 4:
         case 5:
         case 6: {
-            const int warps = smode == 6 ? 3 : smode == 5 ? h->handover_warps : smode == 4 ? 2 : 1;
+            const int warps = smode == 6 ? 3 : smode == 5 ? handover_warps_for(h, N) : smode == 4 ? 2 : 1;
             h->series_kernel_name = std::string(h->n <= 12 ? "grn_series_pirk_kernel<5 Gauss stages x 6 lanes"
                                                             : "grn_series_pirk_kernel<4 Gauss stages x 8 lanes") +
                                     (warps == 3 ? ", three step sizes>" : warps == 2 ? ", two step sizes>" : ">") +
@@ -969,6 +991,17 @@ int lassim_last_kernel_ms(lassim_handle *h, float *ms) {
     CU(guard_.err);
     CU(cudaEventSynchronize(h->ev1));
     CU(cudaEventElapsedTime(ms, h->ev0, h->ev1));
+    return LASSIM_OK;
+}
+
+int lassim_last_stage_parallel_ms(lassim_handle *h, float *ms) {
+    if (!h || !ms) return LASSIM_E_INVALID;
+    if (!h->sp_timed)
+        return fail(h, LASSIM_E_STATE, "the last evaluation did not launch the stage-parallel kernel");
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
+    CU(cudaEventSynchronize(h->ev_sp1));
+    CU(cudaEventElapsedTime(ms, h->ev_sp0, h->ev_sp1));
     return LASSIM_OK;
 }
 

@@ -90,18 +90,20 @@ constexpr size_t pirk_smem_doubles(int S, int LPS, int NC, int warps) {
 }
 
 // Step sizes attempted side by side, as multiples of the controller's proposal, largest
-// first: two warps {1, 0.7} (as in the speculative explicit kernel), three {1.15, 1, 0.7}.
+// first: two warps {1, 0.7} (as in the speculative explicit kernel), three {1.2, 1, 0.7}
+// (CPU study of the two Th2 limit cycles: {1.1, 1, 0.7} 11,930 sequential attempts, {1.15, 1, 0.7}
+// 11,808, {1.2, 1, 0.7} 11,670, {1.25, 1, 0.75} 11,780, four sizes {1, 0.85, 0.7, 0.5} 12,004).
 __host__ __device__ constexpr double pirk_ratio(int WARPS, int role) {
     return WARPS == 2 ? (role == 0 ? 1.0 : 0.7)
-         : WARPS == 3 ? (role == 0 ? 1.15 : role == 1 ? 1.0 : 0.7)
+         : WARPS == 3 ? (role == 0 ? 1.2 : role == 1 ? 1.0 : 0.7)
                       : 1.0;
 }
 
 // WARPS > 1: that many warps per trajectory, on different schedulers.  All carry the same
 // state; each attempts the step from that state at its own multiple of the proposed size; the
 // largest attempt that passes its error test is taken by all of them (a limit cycle rejects
-// 17-25 % of its proposed steps, and a step 15 % above the proposal passes more often than
-// not).  One exchange through shared memory and one named barrier per attempt.
+// 17-25 % of its proposed steps, and a step 20 % above the proposal passes about half the
+// time).  One exchange through shared memory and one named barrier per attempt.
 template <int S, int LPS, int NC, bool FAST, int WARPS = 1>
 __global__ void __launch_bounds__(pirk_threads(WARPS), WARPS == 3 ? 1 : 2)
 grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {

@@ -493,7 +493,7 @@ def test_time_series_kernels_stay_inside_the_error_control(engine, th2, name):
     """Small batches integrate their time series with one warp per trajectory
     (lassim_set_speculation): 'stages' = the stage-parallel Gauss pair, 'stages2' =
     the same with a second warp attempting 0.7 of every step, 'stages3' = three warps
-    attempting 1.15, 1 and 0.7 of it, 'handover' = standard kernel first, time series
+    attempting 1.2, 1 and 0.7 of it, 'handover' = standard kernel first, time series
     over the attempt cap continue in 'stages3' (what
     'auto' picks up to 16,384 candidates), 'on' = the explicit pair with a second,
     shorter attempt in the other half of the warp, 'off' = the standard kernel.  All must pass the parity
