@@ -367,11 +367,11 @@ def run_ours(args):
             "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak,
                          "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
                          # dram__bytes_read.sum + dram__bytes_write.sum of the evaluation's three
-                         # kernels, one ncu --set full capture (profiles/r1_l_ncu_full_summary.txt);
+                         # kernels, one ncu --set full capture (profiles/r1_m_ncu_full_summary.txt);
                          # algorithmic bytes are X in + cost out = 0.72 MB: the path is compute-bound
-                         "traffic": 514048,
-                         "traffic_source": "profiles/r1_l_ncu_full_summary.txt (this kernel; the "
-                                           "evaluation's three kernels together: 2,261,760 bytes)",
+                         "traffic": 514816,
+                         "traffic_source": "profiles/r1_m_ncu_full_summary.txt (this kernel; the "
+                                           "evaluation's three kernels together: 2,266,368 bytes)",
                          "kernel": eng.series_kernel_name(POP), "kernel_ms": d_ms,
                          "attempts_per_launch": series_attempts,
                          "flops_per_attempt": series_flops,
