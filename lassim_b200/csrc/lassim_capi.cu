@@ -230,19 +230,20 @@ void pirk_kernel(int n, KernelChoice *out) {
     }
 }
 
-template <int L>
+template <int L, int R>
 kernel_fn sparse_kernel(int method, int max_deg) {
     if (max_deg <= 8) {
-        if (method == kMethodDOP853) return grn_cost_kernel<L, 2, EllW<2, 8>, kMethodDOP853, true>;
-        return grn_cost_kernel<L, 2, EllW<2, 8>, kMethodDP45, true>;
+        if (method == kMethodDOP853) return grn_cost_kernel<L, R, EllW<R, 8>, kMethodDOP853, true>;
+        return grn_cost_kernel<L, R, EllW<R, 8>, kMethodDP45, true>;
     }
-    if (method == kMethodDOP853) return grn_cost_kernel<L, 2, CsrW<2>, kMethodDOP853, true>;
-    return grn_cost_kernel<L, 2, CsrW<2>, kMethodDP45, true>;
+    if (method == kMethodDOP853) return grn_cost_kernel<L, R, CsrW<R>, kMethodDOP853, true>;
+    return grn_cost_kernel<L, R, CsrW<R>, kMethodDP45, true>;
 }
 
 // Which kernel serves a problem.  n <= 16: 16-lane groups, dense rows; n <= 32:
-// one warp, dense rows; beyond: two genes per lane, ELL rows (in-degree <= 8) or
-// CSR, one warp up to n = 64, a 128-thread CTA up to 256, 512 threads up to 1024.
+// one warp, dense rows; beyond: ELL rows (in-degree <= 8) or CSR, a 64-thread CTA with one
+// gene per lane up to n = 64, two genes per lane in a 128-thread CTA up to 256, 512 threads
+// up to 1024.
 // LASSIM_GROUP=4 selects the 4-lane x 3-gene throughput shape for n <= 12 and
 // LASSIM_EXACT_MATH=1 libm exp + IEEE division instead of the fast logistic
 // (both diagnostics, DP45 only).
@@ -285,9 +286,20 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
         *out = {fn, 32, 1, "dense 32x1"};
         return true;
     }
-    if (n <= 64) { *out = {sparse_kernel<32>(method, h->max_deg), 32, 2, "sparse 32x2"}; return true; }
-    if (n <= 256) { *out = {sparse_kernel<128>(method, h->max_deg), 128, 2, "sparse 128x2"}; return true; }
-    if (n <= 1024) { *out = {sparse_kernel<512>(method, h->max_deg), 512, 2, "sparse 512x2"}; return true; }
+    // 33..64 genes: one gene per lane, a CTA of 64 threads per trajectory.  With two genes per
+    // lane in one warp the kernel is issue-bound on its own FP64 instructions and spills (50
+    // genes: 2.95 us per attempt alone against 1.87; config 3, which waits for one time series of
+    // 24,835 attempts, goes from 114 to 74 ms).  Beyond 64 genes the batches are throughput-bound
+    // and two genes per lane win (200 genes, config 4: 1.09 s against 1.64 s with 256 x 1).
+    // LASSIM_SPARSE_R2=1 brings the one-warp shape back (A/B).
+    const char *r2 = getenv("LASSIM_SPARSE_R2");
+    if (n <= 64) {
+        if (r2 && atoi(r2) != 0) *out = {sparse_kernel<32, 2>(method, h->max_deg), 32, 2, "sparse 32x2"};
+        else *out = {sparse_kernel<64, 1>(method, h->max_deg), 64, 1, "sparse 64x1"};
+        return true;
+    }
+    if (n <= 256) { *out = {sparse_kernel<128, 2>(method, h->max_deg), 128, 2, "sparse 128x2"}; return true; }
+    if (n <= 1024) { *out = {sparse_kernel<512, 2>(method, h->max_deg), 512, 2, "sparse 512x2"}; return true; }
     return false;
 }
 

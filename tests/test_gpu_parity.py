@@ -289,7 +289,7 @@ def random_problem(n, T, seed, density=0.5, pert=False, tmax=10.0):
 @pytest.mark.parametrize("n,T,pert,density", [
     (1, 4, False, 0.5), (2, 3, True, 0.5), (5, 6, True, 0.5), (12, 1, False, 0.5),
     (13, 5, True, 0.5), (16, 4, False, 0.5), (17, 3, True, 0.5), (32, 4, False, 0.5),
-    (33, 3, True, 0.1),      # one warp, two genes per lane, ELL rows
+    (33, 3, True, 0.1),      # 64-thread CTA, one gene per lane, ELL rows
     (40, 3, False, 0.5),     # in-degree > 8: CSR rows
     (64, 3, False, 0.08),
     (70, 3, True, 0.05),     # 128-thread CTA per trajectory
