@@ -9,7 +9,8 @@
 //
 //   L <= 32  the group is a slice of a warp (Th2: 16 lanes, 2 groups per warp);
 //            the step loop is warp-uniform, groups of a warp run in lockstep
-//   L  > 32  the group is a whole CTA of L threads (n = 200: 128 lanes x 2 genes)
+//   L  > 32  the group is a whole CTA of L threads (n = 50: 64 lanes x 1 gene,
+//            n = 200: 128 lanes x 2 genes)
 //
 // Per lane, in registers: its R state entries, the stage derivatives, lambda,
 // vmax and its rows of W (dense for n <= 32, ELL or CSR beyond).  The stage
