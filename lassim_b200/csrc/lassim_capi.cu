@@ -351,8 +351,10 @@ int handover_warps_for(const lassim_handle *h, int N) {
 
 unsigned series_cap_for(const lassim_handle *h, int N) {
     if (h->series_cap != 0u) return h->series_cap;
-    const long long c = 3LL * N / 4;
-    return (unsigned)(c < 500 ? 500 : c > 8000 ? 8000 : c);
+    long long c = 3LL * N / 4;
+    c = c < 500 ? 500 : c > 8000 ? 8000 : c;
+    // the 5(4) pair takes about four attempts where the 8(5,3) pair takes one
+    return (unsigned)(h->method == kMethodDP45 ? 4 * c : c);
 }
 
 int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P,
