@@ -319,6 +319,36 @@ def test_small_and_ragged_problems_match_oracle(engine, n, T, pert, density):
             assert out["cost"][c] == out["cost_main"][c]
 
 
+@pytest.mark.parametrize("n,pert", [(3, False), (12, True), (13, True), (16, False)])
+def test_stage_parallel_kernels_on_small_problems(engine, n, pert):
+    """Both Gauss kernels (5 stages x 6 lanes up to 12 genes, 4 stages x 8 lanes up to 16), with
+    one, two and three warps per trajectory and behind a hand-over after 5 attempts, against
+    the oracle at tight tolerance: same gates as the standard kernel."""
+    p, X = random_problem(n, 5, seed=300 + n, pert=pert)
+    engine.set_tolerances()
+    engine.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"], p["pert"], 0.7)
+    tight = orc.tight_ode()
+    want = [orc.core_cost(x, p["data"], p["sigma"], p["times"], p["y0"], p["vector_map"], p["mask"],
+                          tight, return_traj=True) for x in X]
+    engine.set_speculation("off")
+    base = engine.eval(X, details=True)
+    for mode in ("stages", "stages2", "stages3", "handover"):
+        engine.set_speculation(mode)
+        engine.set_series_cap(5 if mode == "handover" else 0)
+        out = engine.eval(X, details=True)
+        if mode == "handover":
+            assert engine.last_stage_parallel_attempts() > 0
+        Y = engine.trajectories(X)
+        assert (out["status"] == 0).all()
+        for c, (cm, Yt) in enumerate(want):
+            assert out["cost_main"][c] == pytest.approx(cm, rel=COST_RTOL)
+            np.testing.assert_allclose(Y[c], Yt, rtol=TRAJ_RTOL, atol=1e-7)
+        if pert:      # knock-down trajectories do not depend on the time-series kernel
+            np.testing.assert_array_equal(out["pert_cost"], base["pert_cost"])
+    engine.set_series_cap(0)
+    engine.set_speculation("auto")
+
+
 def test_synthetic_50_gene_golden(engine):
     """BASELINE config 3's problem (50 genes, in-degree 5): reference outputs in
     tests/golden/syn50.npz."""
