@@ -398,7 +398,7 @@ def run_ours(args):
             line["other_integrator"] = other
         if world == 1 and not args.no_cpu_baseline:
             arm = CpuArm(p)
-            S = sample_size(arm.cores, 4)
+            S = sample_size(arm.cores, 32)   # about 10 s on 16 cores: includes the slow candidates
             dt, costs = arm.run(X[:S])
             arm.close()
             gpu = cost_h[:S]
