@@ -6,8 +6,8 @@ import subprocess
 PKG = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(PKG, "liblassim_b200.so")
 SOURCES = [os.path.join(PKG, "csrc", "lassim_capi.cu")]
-DEPS = SOURCES + [os.path.join(PKG, "csrc", "grn_kernels.cuh"),
-                  os.path.join(os.path.dirname(PKG), "include", "lassim_b200.h")]
+DEPS = SOURCES + [os.path.join(PKG, "csrc", f) for f in sorted(os.listdir(os.path.join(PKG, "csrc")))
+                  if f.endswith(".cuh")] + [os.path.join(os.path.dirname(PKG), "include", "lassim_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo",
               "-std=c++17", "-shared", "-Xcompiler", "-fPIC"]
 

@@ -100,7 +100,15 @@ constexpr int threads_for(int L) { return L > 32 ? L : (L == 4 ? 256 : 128); }
 #ifndef LASSIM_MIN_BLOCKS
 #define LASSIM_MIN_BLOCKS 4
 #endif
-constexpr int min_blocks_for(int L) { return (L == 16 || L == 32) ? LASSIM_MIN_BLOCKS : 1; }
+// 32-lane groups keep up to 32 weights per lane in registers: at 4 CTAs per SM (128
+// registers) they spill; 2 is faster (2048 candidates, 20 / 24 / 32 genes: 78 -> 65 ms,
+// 104 -> 85, 94 -> 71; tools/gpu_dense32.py)
+#ifndef LASSIM_MIN_BLOCKS_32
+#define LASSIM_MIN_BLOCKS_32 2
+#endif
+constexpr int min_blocks_for(int L) {
+    return L == 16 ? LASSIM_MIN_BLOCKS : L == 32 ? LASSIM_MIN_BLOCKS_32 : 1;
+}
 
 // doubles of shared memory in front of the groups' exchange lines: the 2^(j/256) table
 // (256 entries + the two saturation entries 0 and 2^1000, padded to 264) + 32 of
