@@ -242,8 +242,8 @@ kernel_fn sparse_kernel(int method, int max_deg) {
 
 // Which kernel serves a problem.  n <= 16: 16-lane groups, dense rows; n <= 32:
 // one warp, dense rows; beyond: ELL rows (in-degree <= 8) or CSR, a 64-thread CTA with one
-// gene per lane up to n = 64, two genes per lane in a 128-thread CTA up to 256, 512 threads
-// up to 1024.
+// gene per lane up to n = 64, then two genes per lane in CTAs of 64, 128, 256, 384 and 512
+// threads (n <= 128, 256, 512, 768, 1024).
 // LASSIM_GROUP=4 selects the 4-lane x 3-gene throughput shape for n <= 12 and
 // LASSIM_EXACT_MATH=1 libm exp + IEEE division instead of the fast logistic
 // (both diagnostics, DP45 only).
@@ -298,7 +298,16 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
         else *out = {sparse_kernel<64, 1>(method, h->max_deg), 64, 1, "sparse 64x1"};
         return true;
     }
+    const char *wide = getenv("LASSIM_SPARSE_WIDE");      // A/B: the coarser steps 128 / 512 only
+    const bool fine = !(wide && atoi(wide) != 0);
+    // CTA sizes in steps of 2 (1.5 at the top): idle warps of a CTA-wide group still pay every
+    // barrier (70 genes: 128 x 2 -> 64 x 2 took a batch from 187 to 99 ms; 300 genes: 512 x 2 ->
+    // 256 x 2 from 894 to 514 ms; 600 genes: 512 x 2 -> 384 x 2 from 750 to 618 ms; the
+    // intermediate 96 and 192 gained 2-3 % and were left out)
+    if (n <= 128 && fine) { *out = {sparse_kernel<64, 2>(method, h->max_deg), 64, 2, "sparse 64x2"}; return true; }
     if (n <= 256) { *out = {sparse_kernel<128, 2>(method, h->max_deg), 128, 2, "sparse 128x2"}; return true; }
+    if (n <= 512 && fine) { *out = {sparse_kernel<256, 2>(method, h->max_deg), 256, 2, "sparse 256x2"}; return true; }
+    if (n <= 768 && fine) { *out = {sparse_kernel<384, 2>(method, h->max_deg), 384, 2, "sparse 384x2"}; return true; }
     if (n <= 1024) { *out = {sparse_kernel<512, 2>(method, h->max_deg), 512, 2, "sparse 512x2"}; return true; }
     return false;
 }

@@ -292,9 +292,11 @@ def random_problem(n, T, seed, density=0.5, pert=False, tmax=10.0):
     (33, 3, True, 0.1),      # 64-thread CTA, one gene per lane, ELL rows
     (40, 3, False, 0.5),     # in-degree > 8: CSR rows
     (64, 3, False, 0.08),
-    (70, 3, True, 0.05),     # 128-thread CTA per trajectory
-    (150, 2, False, 0.2),    # CSR rows in a CTA-wide group
-    (300, 2, False, 0.01),   # 512-thread CTA per trajectory
+    (70, 3, True, 0.05),     # 64-thread CTA, two genes per lane
+    (150, 2, False, 0.2),    # CSR rows in a 128-thread CTA
+    (300, 2, False, 0.01),   # 256-thread CTA per trajectory
+    (520, 2, False, 0.006),  # 384-thread CTA per trajectory
+    (800, 2, False, 0.004),  # 512-thread CTA per trajectory
 ])
 def test_small_and_ragged_problems_match_oracle(engine, n, T, pert, density):
     p, X = random_problem(n, T, seed=100 + n, density=density, pert=pert)
