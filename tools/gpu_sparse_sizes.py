@@ -5,7 +5,7 @@ REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, REPO); sys.path.insert(0, os.path.join(REPO, "tools"))
 from lassim_b200._capi import Engine
 from workloads import synthetic_problem, uniform_population
-for n, N in ((70, 512), (150, 256), (200, 128), (300, 64), (600, 16)):
+for n, N in [(int(a), int(b)) for a, b in (x.split(':') for x in sys.argv[1:])] or ((70, 512), (150, 256), (200, 128), (300, 64), (600, 16)):
     p = synthetic_problem(n, seed=n)
     X = uniform_population(p["lb"], p["ub"], N, seed=1)
     eng = Engine(0)
