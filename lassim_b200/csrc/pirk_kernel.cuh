@@ -311,6 +311,10 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
         // attempts left in the budget, counted down in a register (comparing with the kernel
         // parameter would reload it from the constant bank at the end of every attempt)
         unsigned budget_left = P.max_steps;
+        if (B.resume) {                // what the standard kernel used before the hand-over counts
+            const unsigned used = B.traj_steps[(size_t)c * P.K];
+            budget_left = used < budget_left ? budget_left - used : 1u;
+        }
         asm volatile("" : "+r"(budget_left));
         while (left > 0) {
             // ------------------------------------------------ one attempt

@@ -482,6 +482,15 @@ def test_step_budget_is_reported_not_hung(engine, th2, th2_uniform):
     engine.set_tolerances()
     assert (out["status"] & ST_STEP_BUDGET).all()
     assert np.isnan(out["cost"]).all()
+    # the budget spans both kernels of a handed-over time series: 300 attempts in the standard
+    # kernel, then at most 100 more in the stage-parallel one
+    bind_th2(engine, th2, pert=False)
+    engine.set_tolerances(max_steps=400)
+    engine.set_speculation("handover"); engine.set_series_cap(300)
+    out = engine.eval(th2_uniform["X"][:8], details=True)
+    steps = engine.last_traj_steps(8)[:, 0]
+    engine.set_series_cap(0); engine.set_speculation("auto"); engine.set_tolerances()
+    assert (out["status"] & ST_STEP_BUDGET).all() and (steps <= 400).all() and (steps > 300).all()
     from lassim_b200.core.core_problem import CoreProblemFactory
     from lassim_b200.core.functions.common_functions import odeint1e8_lassim
     # through the problem class such candidates cost +inf
