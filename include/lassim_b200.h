@@ -107,24 +107,30 @@ int lassim_set_method(lassim_handle *h, int method);
  *   4  the same with a second warp attempting 0.7 of every step (as in 1)
  *   6  the same with three warps attempting 1.2, 1 and 0.7 of the proposed step
  *      (the largest that passes its error test is taken)
- *   5  hand-over: every time series starts in the standard kernel; those still
- *      going after a cap of attempts (three per four candidates of the batch, within
- *      [500, 8000]; LASSIM_SERIES_CAP in the environment overrides) stop at the
- *      step they are on and continue in kernel 6 (512 to 8192 candidates) or 4,
- *      launched behind it on the same stream.  The many short time series stay cheap, the few long ones get the
- *      fast kernel almost to themselves
- *   2  automatic (default): 5 for batches of at most 16,384 candidates, else 0
- * Results are deterministic for a given mode and batch size and stay inside the
- * same error control; with 5 a candidate's time series depends on the batch size
- * through the cap (at the level of the integration tolerance).  The knock-down
- * trajectories always run on the standard kernel, concurrently on a second
- * stream.  (No reference counterpart.)  LASSIM_SPECULATE in the environment
+ *   5  hand-over: every time series starts in the standard kernel; one that looks long
+ *      (lassim_set_handover_rule) stops at the step it is on and continues in kernel 6
+ *      (kernel 4 with LASSIM_HANDOVER_WARPS=2 in the environment), launched behind it on
+ *      the same stream.  The many short time series stay cheap, the few long ones get
+ *      the fast kernel almost to themselves
+ *   2  automatic (default): 5 wherever the stage-parallel kernel exists (n <= 16)
+ * Results are deterministic for a given mode and stay inside the same error control.
+ * Neither the automatic choice nor the hand-over rule looks at the batch: a candidate
+ * costs the same evaluated alone (a batch of one, _objfun_impl) as among 100,000 others.
+ * The knock-down trajectories always run on the standard kernel, concurrently on a
+ * second stream.  (No reference counterpart.)  LASSIM_SPECULATE in the environment
  * sets the initial mode. */
 int lassim_set_speculation(lassim_handle *h, int mode);
 
-/* Attempts a time series makes in the standard kernel before mode 5 hands it
- * over; 0 (default) = automatic, three per four candidates of the batch within
- * [500, 8000].  (No reference counterpart.) */
+/* Which time series mode 5 hands over.  Automatic rule (default 128, 1500, 3000): a time
+ * series leaves the standard kernel when, after at least `min_attempts` attempts, the
+ * time still to cover is more than `remaining_steps` steps of the size its controller
+ * proposes now, or when it has made `max_attempts` attempts.  (Numbers for the 8(5,3)
+ * pair; the 5(4) pair, which takes about four attempts where that one takes one, uses
+ * four times each.)  lassim_set_series_cap(attempts > 0) replaces the rule by a plain cap
+ * - hand over after exactly that many attempts - and 0 brings the rule back.  The rule
+ * sees one trajectory, never the batch.  (No reference counterpart.) */
+int lassim_set_handover_rule(lassim_handle *h, unsigned int min_attempts,
+                             double remaining_steps, unsigned int max_attempts);
 int lassim_set_series_cap(lassim_handle *h, unsigned int attempts);
 
 /* Current decision-vector length (2n + nnz), trajectories per candidate
@@ -209,11 +215,26 @@ int lassim_peripheral_trajectories(lassim_handle *h, int N, const int *gene,
  *                    are dealt round-robin to ranks) takes its two neighbours'
  *                    bests, each replacing the island's worst if strictly better
  *   lassim_de_set_individual  seed one individual (e.g. a known solution)
+ *   lassim_de_set_island_ids  where this GPU's islands sit in the whole archipelago
+ *                    (local island j is island first_island + j * stride): keys the
+ *                    random streams so that islands on different GPUs draw different
+ *                    numbers from one seed.  Default 0, 1.
+ *   lassim_de_set_lanes  islands do not wait for each other inside an evolve round
+ *                    (PyGMO evolves each island in a worker of its own and joins at the
+ *                    end, base_optimization.py:173-174): the islands are split into
+ *                    `lanes` groups, each advancing through its generations on its own
+ *                    stream with its own scratch; a slow candidate holds up its own
+ *                    island's next generation only.  0 = automatic (one island per lane,
+ *                    at most 16 lanes); 1 = all islands in lockstep.  The result does not
+ *                    depend on the number of lanes.  LASSIM_DE_LANES in the environment
+ *                    sets the initial value.
  */
 int lassim_de_init(lassim_handle *h, int islands, int individuals, int variant, double f,
                    double cr, unsigned long long seed, const double *lb, const double *ub,
                    const double *X0);
 int lassim_de_set_individual(lassim_handle *h, int island, int index, const double *x);
+int lassim_de_set_island_ids(lassim_handle *h, int first_island, int stride);
+int lassim_de_set_lanes(lassim_handle *h, int lanes);
 int lassim_de_evolve(lassim_handle *h, int generations);
 int lassim_de_best(lassim_handle *h, double *table);
 int lassim_de_migrate_ring(lassim_handle *h, const double *table, int n_table, int first_island,

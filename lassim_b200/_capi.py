@@ -38,6 +38,10 @@ def load_library():
         raise LassimError(
             "liblassim_b200.so is not built (%s); run `python -m "
             "lassim_b200.build` - there is no CPU fallback" % _LIB_PATH)
+    # islands evolve concurrently on up to 16 x 2 streams: with the default of 8 hardware
+    # queues streams would share queues and wait for each other.  Only read when the CUDA
+    # context is created, so a host that initialised CUDA earlier keeps its own setting.
+    os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
     lib = ctypes.CDLL(_LIB_PATH)
     H = ctypes.c_void_p
     lib.lassim_version.restype = ctypes.c_char_p
@@ -55,6 +59,8 @@ def load_library():
     lib.lassim_set_speculation.restype = ctypes.c_int
     lib.lassim_set_series_cap.argtypes = [H, ctypes.c_uint]
     lib.lassim_set_series_cap.restype = ctypes.c_int
+    lib.lassim_set_handover_rule.argtypes = [H, ctypes.c_uint, ctypes.c_double, ctypes.c_uint]
+    lib.lassim_set_handover_rule.restype = ctypes.c_int
     lib.lassim_set_method.argtypes = [H, ctypes.c_int]
     lib.lassim_set_method.restype = ctypes.c_int
     lib.lassim_dim.argtypes = [H]
@@ -84,12 +90,15 @@ def load_library():
                                    c_double_p]
     lib.lassim_de_set_individual.argtypes = [H, ctypes.c_int, ctypes.c_int, c_double_p]
     lib.lassim_de_evolve.argtypes = [H, ctypes.c_int]
+    lib.lassim_de_set_island_ids.argtypes = [H, ctypes.c_int, ctypes.c_int]
+    lib.lassim_de_set_lanes.argtypes = [H, ctypes.c_int]
     lib.lassim_de_best.argtypes = [H, c_double_p]
     lib.lassim_de_migrate_ring.argtypes = [H, c_double_p, ctypes.c_int, ctypes.c_int, ctypes.c_int]
     lib.lassim_de_get.argtypes = [H, c_double_p, c_double_p]
     lib.lassim_de_evaluations.argtypes = [H]
     lib.lassim_de_evaluations.restype = ctypes.c_longlong
     for name in ("lassim_de_init", "lassim_de_set_individual", "lassim_de_evolve",
+                 "lassim_de_set_island_ids", "lassim_de_set_lanes",
                  "lassim_de_best", "lassim_de_migrate_ring", "lassim_de_get"):
         getattr(lib, name).restype = ctypes.c_int
     lib.lassim_last_end_states.argtypes = [H, ctypes.c_int, c_double_p]
@@ -205,8 +214,7 @@ class Engine:
         (speculative half-warp attempts), 'stages' (stage-parallel Gauss pair, one warp
         per trajectory), 'stages2' / 'stages3' (the same with two / three warps attempting
         different step sizes), 'handover' (standard kernel first, long time series continue
-        in 'stages3') or 'auto'
-        ('handover' up to 16,384 candidates, 'off' beyond)."""
+        in 'stages3') or 'auto' ('handover' wherever the stage-parallel kernel exists)."""
         code = {"off": 0, "on": 1, "auto": 2, "stages": 3, "stages2": 4, "handover": 5, "stages3": 6,
                 0: 0, 1: 1, 2: 2, 3: 3, 4: 4, 5: 5, 6: 6, False: 0, True: 1}.get(mode)
         if code is None:
@@ -215,9 +223,16 @@ class Engine:
         self._check(self._lib.lassim_set_speculation(self._h, code), "lassim_set_speculation")
 
     def set_series_cap(self, attempts=0):
-        """Attempts a time series makes in the standard kernel before 'handover' moves it
-        to the stage-parallel kernel; 0 = automatic."""
+        """Plain cap: 'handover' moves a time series to the stage-parallel kernel after
+        exactly this many attempts; 0 = the automatic rule (set_handover_rule)."""
         self._check(self._lib.lassim_set_series_cap(self._h, int(attempts)), "lassim_set_series_cap")
+
+    def set_handover_rule(self, min_attempts=128, remaining_steps=1500.0, max_attempts=3000):
+        """'handover' moves a time series when, after min_attempts attempts, more than
+        remaining_steps steps of its current size are still ahead, or at max_attempts."""
+        self._check(self._lib.lassim_set_handover_rule(self._h, int(min_attempts),
+                                                       float(remaining_steps), int(max_attempts)),
+                    "lassim_set_handover_rule")
 
     def set_method(self, method="dop853"):
         """'dop853' (Dormand-Prince 8(5,3), default) or 'dp45' (Dormand-Prince 5(4))."""
@@ -371,6 +386,16 @@ class Engine:
             raise ValueError("individual of length %d for dimension %d" % (x.size, self.dim))
         self._check(self._lib.lassim_de_set_individual(self._h, int(island), int(index), _dp(x)),
                     "lassim_de_set_individual")
+
+    def de_set_island_ids(self, first_island=0, stride=1):
+        """Position of this GPU's islands in the whole archipelago (keys the random streams)."""
+        self._check(self._lib.lassim_de_set_island_ids(self._h, int(first_island), int(stride)),
+                    "lassim_de_set_island_ids")
+
+    def de_set_lanes(self, lanes=0):
+        """Groups of islands that evolve concurrently on streams of their own (0 = automatic,
+        1 = all islands in lockstep); does not change results."""
+        self._check(self._lib.lassim_de_set_lanes(self._h, int(lanes)), "lassim_de_set_lanes")
 
     def de_evolve(self, generations):
         self._check(self._lib.lassim_de_evolve(self._h, int(generations)), "lassim_de_evolve")

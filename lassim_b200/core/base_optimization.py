@@ -8,6 +8,16 @@ from sortedcontainers import SortedList
 import os
 
 from ..pygmo import archipelago, device_archipelago, island, topology
+from ..pygmo.archipelago import _dist
+
+
+def _dist_active():
+    return _dist() is not None
+
+
+def _dist_rank():
+    d = _dist()
+    return d.get_rank() if d is not None else 0
 
 
 class BaseOptimization:
@@ -84,9 +94,13 @@ class BaseOptimization:
             self._logger.info("BaseOptimization completed.")
         except Exception:
             self._logger.exception("Exception occurred during execution...")
-        finally:
-            self._logger.info("Returning solutions found.")
-            return solutions
+            if _dist_active():
+                # one process per GPU: the other ranks are waiting in the next migration
+                # all-reduce; returning partial solutions here would leave them there.
+                # Let the failure end this process so the launcher stops the job.
+                raise
+        self._logger.info("Returning solutions found.")
+        return solutions
 
     def _generate_solution(self, prob, reactions, topol):
         archi = self._generate_archipelago(prob, topol)
@@ -94,7 +108,9 @@ class BaseOptimization:
         archi.join()
         self.evaluations += archi.evaluations
         solutions = self._get_solutions(archi, prob, reactions)
-        self._handler.handle_solutions(solutions)
+        # every rank holds every island's champion after join(); the files are written once
+        if not _dist_active() or _dist_rank() == 0:
+            self._handler.handle_solutions(solutions)
         return solutions[0]
 
     def _generate_archipelago(self, prob, topol):

@@ -17,6 +17,13 @@ struct DeParams {
     double f, cr;
     unsigned long long seed;
     unsigned long long generation;   // advances the random stream
+    // position of this GPU's islands in the whole archipelago (local island j is island
+    // gid_base + j * gid_stride): keys the random streams, so that islands on different
+    // GPUs draw different numbers from the same seed
+    int gid_base = 0, gid_stride = 1;
+    // individuals [ind_begin, ind_end) of the islands * np this launch works on (a lane of
+    // the asynchronous evolve handles a group of consecutive islands)
+    int ind_begin = 0, ind_end = 0;
 };
 
 // cost with "worse than anything" for NaN
@@ -26,14 +33,19 @@ __device__ __forceinline__ double de_key(double v) { return (v != v) ? CUDART_IN
 __global__ void de_trial_kernel(const DeParams p, const double *__restrict__ X,
                                 const double *__restrict__ F, const double *__restrict__ lb,
                                 const double *__restrict__ ub, double *__restrict__ trial) {
-    const int gi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (gi >= p.islands * p.np) return;
+    const int gi = p.ind_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (gi >= p.ind_end) return;
     const int isl = gi / p.np, i = gi - isl * p.np;
     const int NP = p.np, D = p.dim;
     const double *Xi = X + (size_t)isl * NP * D;
     const double *Fi = F + (size_t)isl * NP;
+    // one Philox subsequence per individual of the whole archipelago; a generation draws at
+    // most 5 partners (+ rare repeats), one start index, D crossover uniforms and D redraws,
+    // two 32-bit numbers per double: the stream advances by 4 D + 64 per generation
     curandStatePhilox4_32_10_t rng;
-    curand_init(p.seed, (unsigned long long)gi, p.generation * 4096ull, &rng);
+    const unsigned long long gisl = (unsigned long long)(p.gid_base + isl * p.gid_stride);
+    curand_init(p.seed, gisl * (unsigned long long)NP + (unsigned long long)i,
+                p.generation * (unsigned long long)(4 * D + 64), &rng);
 
     int best = 0;
     double fb = de_key(Fi[0]);
@@ -99,11 +111,13 @@ __global__ void de_mask_status_kernel(int count, const int *__restrict__ status,
     if (i < count && status[i] != 0) cost[i] = CUDART_INF;
 }
 
+// Ft[0 .. ind_end - ind_begin): costs of the trials of individuals [ind_begin, ind_end)
 __global__ void de_select_kernel(const DeParams p, double *__restrict__ X, double *__restrict__ F,
                                  const double *__restrict__ trial, const double *__restrict__ Ft) {
-    const int gi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (gi >= p.islands * p.np) return;
-    const double ft = Ft[gi];
+    const int li = blockIdx.x * blockDim.x + threadIdx.x;
+    const int gi = p.ind_begin + li;
+    if (gi >= p.ind_end) return;
+    const double ft = Ft[li];
     if (ft < F[gi]) {            // false for NaN: NaN never wins
         F[gi] = ft;
         const double *t = trial + (size_t)gi * p.dim;

@@ -76,11 +76,15 @@ struct DevBatch {
     unsigned int work_begin;  // this launch serves work items [work_begin, work_begin + work_count)
     unsigned int work_count;  //   of the N*K items (item w: trajectory w / N of candidate w % N)
     // Hand-over of long time series (see launch_kernels): with series_cap > 0 a time series
-    // that has used that many attempts stops at the step it is on, leaves its state behind
+    // that has used that many attempts - or, from ho_min attempts on, has more than ho_rem
+    // steps of the size its controller now proposes ahead of it: a rule that looks at the
+    // trajectory alone, never at the batch - stops at the step it is on, leaves its state behind
     // (y in the last row of its Y block, t in cost_main, h in pert_cost) and appends
     // (sample index << 32 | candidate) to long_list; the stage-parallel kernel launched
     // behind it with resume = 1 takes its work items from that list.
-    unsigned int series_cap = 0;
+    unsigned int series_cap = 0;           // hand over after this many attempts, whatever else
+    unsigned int ho_min = 0xffffffffu;     // or after ho_min attempts when more than ho_rem steps
+    double ho_rem = 0.0;                   //   of the current size are still ahead
     int resume = 0;
     unsigned int *long_count = nullptr;        // zeroed before launch
     unsigned long long *long_list = nullptr;   // [N]
@@ -487,6 +491,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
     unsigned nacc = 0, nrej = 0;
     bool rejected = false;
     double t = 0.0, h = 0.0, tend = 0.0;
+    double tfin = 0.0;     // last sample time of the trajectory (hand-over rule)
     const double *tl = P.times;
 
     // sigmoid(W in) = sr + sr*se: publish this lane's entries, barrier, mat-vec, logistic
@@ -575,6 +580,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                 t = tl[0];
                 ti = 1;
                 tend = (nt > 1) ? tl[1] : t;
+                if constexpr (HANDOVER) tfin = tl[nt - 1];
                 nacc = 0; nrej = 0; rejected = false; st = 0;
                 if (k == 0) {
                     double *Yc = B.Y + (size_t)c * P.T * n;
@@ -738,9 +744,12 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
 
         // a time series over its attempt cap is handed to the kernel behind this one
         bool handover = false;
-        if constexpr (HANDOVER)
+        if constexpr (HANDOVER) {
+            const unsigned att = nacc + nrej;
             handover = active && k == 0 && B.series_cap != 0u && ti < nt && st == 0 &&
-                       nacc + nrej >= B.series_cap;
+                       (att >= B.series_cap ||
+                        (att >= B.ho_min && tfin - t > B.ho_rem * h));
+        }
         if (active && (ti >= nt || handover)) {
             // ------------------------------------------------------ epilogue
             if (handover) {

@@ -11,7 +11,9 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <string>
+#include <tuple>
 #include <vector>
 
 using namespace lassim;
@@ -35,21 +37,75 @@ struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
+// Hand-over of long time series, automatic rule.  A time series leaves the standard kernel
+// for the stage-parallel one when, after at least kHandoverMinAttempts attempts, the time
+// still to cover is more than kHandoverRemaining steps of the size its controller proposes
+// now - or, whatever its steps look like, when it has made kHandoverMaxAttempts attempts.
+// The rule looks at the trajectory alone, never at the batch, so a candidate's result does
+// not depend on which other candidates are evaluated with it.
+constexpr unsigned kHandoverMinAttempts = 128;
+constexpr double kHandoverRemaining = 1500.0;
+constexpr unsigned kHandoverMaxAttempts = 3000;
+
 }  // namespace
+
+// Everything ONE evaluation in flight writes to besides the caller's buffers, with the
+// auxiliary stream its knock-down trajectories run on.  The handle owns one for the
+// evaluation entry points and one per lane of the on-device differential evolution
+// (islands evolve concurrently, each lane on its own stream with its own scratch).
+struct Scratch {
+    DevBuf<double> cost, cost_main, pert_cost, Y, E;
+    DevBuf<unsigned char> zero;   // work counters | done | status | counters
+    DevBuf<unsigned int> steps;
+    DevBuf<unsigned long long> long_list;   // hand-over list of long time series
+    cudaStream_t aux = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaError_t init(int prio) {
+        cudaError_t e = cudaStreamCreateWithPriority(&aux, cudaStreamNonBlocking, prio);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming);
+        return e;
+    }
+    void release() {
+        cost.release(); cost_main.release(); pert_cost.release(); Y.release(); E.release();
+        zero.release(); steps.release(); long_list.release();
+        if (ev_fork) cudaEventDestroy(ev_fork);
+        if (ev_join) cudaEventDestroy(ev_join);
+        if (aux) cudaStreamDestroy(aux);
+        ev_fork = ev_join = nullptr; aux = nullptr;
+    }
+};
+
+// One lane of the on-device differential evolution: a group of consecutive islands that
+// advances through its generations on its own stream.
+struct DeLane {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_done = nullptr;
+    Scratch scratch;
+    int first = 0, count = 0;     // local islands [first, first + count)
+};
 
 struct lassim_handle {
     int device = 0;
     int sm_count = 0;
-    cudaStream_t stream = nullptr, stream2 = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr;
+    int prio_lo = 0, prio_hi = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t ev_sp0 = nullptr, ev_sp1 = nullptr;   // around the stage-parallel kernel
     bool sp_timed = false;
     int speculate = 2;        // lassim_set_speculation mode (2 = automatic)
-    unsigned series_cap = 0;      // hand-over cap; 0 = automatic (series_cap_for)
-    int handover_warps = 0;       // warps per trajectory of the kernel long time series move to; 0 = by batch size
+    // Hand-over of long time series (series_rule below): hard cap of attempts in the
+    // standard kernel (0 = the automatic rule), and the automatic rule's three numbers
+    unsigned series_cap = 0;
+    unsigned ho_min = kHandoverMinAttempts, ho_max = kHandoverMaxAttempts;
+    double ho_rem = kHandoverRemaining;
+    int handover_warps = 0;       // warps per trajectory of the kernel long time series move to; 0 = three
     bool timed = false;
     std::string err, kernel_name, series_kernel_name;
     long long launches = 0;
+    // resident CTAs per SM of every (kernel, CTA size, dynamic shared memory) launched so far:
+    // the attribute call and the occupancy query are made once per shape, not per launch
+    std::map<std::tuple<const void *, int, size_t>, int> per_sm_cache;
 
     // problem (host copies)
     bool has_problem = false;
@@ -70,11 +126,9 @@ struct lassim_handle {
     DevBuf<unsigned char> d_pmask;
     DevBuf<int> d_pgene;
 
-    // scratch
-    DevBuf<double> d_X, d_cost, d_cost_main, d_pert_cost, d_Y, d_E, d_probe;
-    DevBuf<unsigned char> d_zero;   // work counter | done | status | counters
-    DevBuf<unsigned int> d_steps;
-    DevBuf<unsigned long long> d_long;   // hand-over list of long time series
+    // scratch of the evaluation entry points
+    DevBuf<double> d_X, d_probe;
+    Scratch main;
     int last_N = 0;
     bool last_had_E = false;
 
@@ -83,6 +137,9 @@ struct lassim_handle {
     DeParams de{};
     long long de_evaluations = 0;
     DevBuf<double> de_X, de_F, de_trial, de_best, de_table, de_lb, de_ub;
+    int de_lanes_wanted = 0;             // 0 = automatic (lassim_de_set_lanes)
+    std::vector<DeLane> de_lanes;
+    cudaEvent_t ev_de_fork = nullptr;
 };
 
 namespace {
@@ -322,21 +379,14 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
 // `s` waits for both.
 // Which kernel integrates the time series of a batch of N candidates:
 // 0 the standard one, 1 speculative, 3 stage-parallel (lassim_set_speculation).
-// Automatic (2): hand-over (5) wherever the stage-parallel kernel exists (n <= 16) up to 16,384
-// candidates, the standard kernel alone beyond.  Measured on Th2 populations
-// (tools/gpu_series_sweep.py, tools/gpu_handover_sweep.py; ms per evaluation):
-//        N   standard  speculative  stage-par.  st.-par. x2   hand-over (cap)
-//       64     30.8       23.0        17.5        14.3        14.8  (500)
-//      256     31.1       23.3        19.0        17.2        16.8  (500)
-//     1024     35.2       25.8        22.6-24.1   23.1-24.1   22.0  (500-2000)
-//     4096     41.1       33.5        35.8        46.0        29.7  (4000)
-//     8192     49.7       47.4        54.3        78.5        41.6  (8000)
-//    16384     69.6        -           -           -          65.7  (4000)
-//    65536    176.4        -           -           -         193.4  (8000)
+// Automatic (2): hand-over (5) wherever the stage-parallel kernel exists (n <= 16), for
+// every batch size: the choice - like the hand-over rule itself - must not depend on N, or
+// a candidate's cost would depend on the company it is evaluated in.
 int series_mode(const lassim_handle *h, const KernelChoice &kc, int N, bool periph) {
+    (void)N;
     if (periph) return 0;
     const bool automatic = h->speculate == 2;
-    if (kc.fn_pirk2 != nullptr && (h->speculate == 5 || (automatic && N <= 16384))) return 5;
+    if (kc.fn_pirk3 != nullptr && (h->speculate == 5 || automatic)) return 5;
     if (kc.fn_pirk3 != nullptr && h->speculate == 6) return 6;
     if (kc.fn_pirk2 != nullptr && h->speculate == 4) return 4;
     if (kc.fn_pirk != nullptr && h->speculate == 3) return 3;
@@ -344,56 +394,60 @@ int series_mode(const lassim_handle *h, const KernelChoice &kc, int N, bool peri
     return 0;
 }
 
-// Attempts a time series gets in the standard kernel before it is handed over: enough that
-// the many short ones finish there (their hand-over would crowd the stage-parallel kernel),
-// few enough that the long ones lose little time at the slower pace.  Measured optimum
-// (table above; 1024 candidates: 300 -> 23.8 ms, 500 -> 22.9, 750 -> 22.5, 1000 -> 22.8,
-// 1500 -> 23.4, 3000 -> 26.4, medians): three attempts per four candidates, within [500, 8000].
-// Warps per handed-over trajectory.  Three step sizes pay where the batch waits for limit
-// cycles in a stage-parallel kernel that is not crowded (medians, ms, two / three warps, two
-// populations each: 64 candidates 14.8 / 16.8 and 11.7 / 13.4; 256: 16.9 / 17.8 and 15.3 / 14.6;
-// 1024: 22.6 / 21.7 and 28.7 / 27.2; 4096: 33.1 / 30.9; 16,384: 60.6 / 62.4).
+// Warps per handed-over trajectory: three step sizes per attempt (two on request,
+// LASSIM_HANDOVER_WARPS=2).  Round 1 picked two below 512 and above 8192 candidates for a
+// few per cent; that made results depend on the batch size and is gone.
 int handover_warps_for(const lassim_handle *h, int N) {
-    if (h->handover_warps == 2 || h->handover_warps == 3) return h->handover_warps;
-    return (N >= 512 && N <= 8192) ? 3 : 2;
+    (void)N;
+    return h->handover_warps == 2 ? 2 : 3;
 }
 
-unsigned series_cap_for(const lassim_handle *h, int N) {
-    if (h->series_cap != 0u) return h->series_cap;
-    long long c = 3LL * N / 4;
-    c = c < 500 ? 500 : c > 8000 ? 8000 : c;
-    // the 5(4) pair takes about four attempts where the 8(5,3) pair takes one
-    return (unsigned)(h->method == kMethodDP45 ? 4 * c : c);
+// The numbers of the hand-over rule for one launch: an explicit cap (lassim_set_series_cap)
+// switches the projection off; otherwise the automatic rule (see kHandover* above).  The
+// 5(4) pair takes about four attempts where the 8(5,3) pair takes one.
+struct SeriesRule { unsigned cap, min_attempts; double remaining; };
+SeriesRule series_rule(const lassim_handle *h) {
+    const unsigned mult = h->method == kMethodDP45 ? 4u : 1u;
+    if (h->series_cap != 0u) return {h->series_cap * mult, 0xffffffffu, 0.0};
+    return {h->ho_max * mult, h->ho_min * mult, h->ho_rem * mult};
 }
 
 int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P,
                    const DevBatch &B, int N, int traj_per_candidate, bool periph,
-                   cudaStream_t s, unsigned int *counters) {
-    // time-series kernel of a small batch: 3 = stage-parallel, 1 = speculative, 2 = auto
-    // (stage-parallel where built, for batches of at most 2048 candidates)
+                   cudaStream_t s, unsigned int *counters, const Scratch &sc, bool time_it) {
+    // time-series kernel of the batch (series_mode above)
     const int smode = series_mode(h, kc, N, periph);
     const kernel_fn series_fn = smode == 6 ? kc.fn_pirk3 : smode >= 4 ? kc.fn_pirk2 : smode == 3 ? kc.fn_pirk
                               : smode == 1 ? kc.fn_shadow : nullptr;
     const bool speculate = series_fn != nullptr;
     auto launch = [&](kernel_fn fn, int threads, size_t smem, int lanes_per_item, unsigned begin,
                       unsigned count, unsigned int *counter, cudaStream_t st,
-                      unsigned series_cap = 0u, int resume = 0) -> cudaError_t {
+                      const SeriesRule *rule = nullptr, int resume = 0) -> cudaError_t {
         if (count == 0) return cudaSuccess;
         const int items_per_cta = threads / lanes_per_item;
-        cudaError_t e = cudaFuncSetAttribute((const void *)fn,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
+        cudaError_t e;
         int per_sm = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem);
-        if (e != cudaSuccess) return e;
-        if (per_sm < 1) per_sm = 1;
+        const auto key = std::make_tuple((const void *)fn, threads, smem);
+        const auto hit = h->per_sm_cache.find(key);
+        if (hit != h->per_sm_cache.end()) {
+            per_sm = hit->second;
+        } else {
+            e = cudaFuncSetAttribute((const void *)fn,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return e;
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem);
+            if (e != cudaSuccess) return e;
+            if (per_sm < 1) per_sm = 1;
+            h->per_sm_cache[key] = per_sm;
+        }
         long long blocks = ((long long)count + items_per_cta - 1) / items_per_cta;
         const long long resident = (long long)h->sm_count * per_sm;
         if (blocks > resident) blocks = resident;
         if (blocks < 1) blocks = 1;
         DevBatch Bl = B;
         Bl.work_begin = begin; Bl.work_count = count; Bl.work_counter = counter;
-        Bl.series_cap = series_cap; Bl.resume = resume; Bl.long_count = counters + 2;
+        if (rule) { Bl.series_cap = rule->cap; Bl.ho_min = rule->min_attempts; Bl.ho_rem = rule->remaining; }
+        Bl.resume = resume; Bl.long_count = counters + 2;
         Bl.sp_attempts = reinterpret_cast<unsigned long long *>(counters + 4);
         fn<<<(unsigned)blocks, threads, smem, st>>>(P, Bl);
         h->launches += 1;
@@ -402,28 +456,29 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
     const int threads = threads_for(kc.L);
     const size_t smem = smem_bytes(kc);
     const unsigned total = (unsigned)N * (unsigned)traj_per_candidate;
-    h->sp_timed = false;
+    if (time_it) h->sp_timed = false;
     if (speculate) {
         const unsigned rest = total - (unsigned)N;
         if (rest > 0) {
-            CU(cudaEventRecord(h->ev_fork, s));
-            CU(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
+            CU(cudaEventRecord(sc.ev_fork, s));
+            CU(cudaStreamWaitEvent(sc.aux, sc.ev_fork, 0));
         }
         if (smode == 5) {
-            // every time series starts in the standard kernel; the ones still going after
-            // series_cap attempts continue in the two-warp stage-parallel kernel behind it
-            CU(launch(kc.fn_capped, threads, smem, kc.L, 0u, (unsigned)N, counters, s, series_cap_for(h, N), 0));
-            CU(cudaEventRecord(h->ev_sp0, s));
+            // every time series starts in the standard kernel; the ones the hand-over rule
+            // picks continue in the multi-warp stage-parallel kernel behind it
+            const SeriesRule rule = series_rule(h);
+            CU(launch(kc.fn_capped, threads, smem, kc.L, 0u, (unsigned)N, counters, s, &rule, 0));
+            if (time_it) CU(cudaEventRecord(h->ev_sp0, s));
             if (handover_warps_for(h, N) == 3)
                 CU(launch(kc.fn_pirk3, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters + 3,
-                          s, 0u, 1));
+                          s, nullptr, 1));
             else
                 CU(launch(kc.fn_pirk2, pirk_threads(2), kc.pirk2_smem, 64, 0u, (unsigned)N, counters + 3,
-                          s, 0u, 1));
+                          s, nullptr, 1));
         } else if (smode == 1) {
             CU(launch(series_fn, threads, smem, 32, 0u, (unsigned)N, counters, s));
         } else {
-            CU(cudaEventRecord(h->ev_sp0, s));
+            if (time_it) CU(cudaEventRecord(h->ev_sp0, s));
             if (smode == 6)
                 CU(launch(series_fn, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters, s));
             else if (smode == 4)
@@ -431,14 +486,14 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
             else
                 CU(launch(series_fn, pirk_threads(1), kc.pirk_smem, 32, 0u, (unsigned)N, counters, s));
         }
-        if (smode != 1) {
+        if (smode != 1 && time_it) {
             CU(cudaEventRecord(h->ev_sp1, s));
             h->sp_timed = true;
         }
         if (rest > 0) {
-            CU(launch(kc.fn, threads, smem, kc.L, (unsigned)N, rest, counters + 1, h->stream2));
-            CU(cudaEventRecord(h->ev_join, h->stream2));
-            CU(cudaStreamWaitEvent(s, h->ev_join, 0));
+            CU(launch(kc.fn, threads, smem, kc.L, (unsigned)N, rest, counters + 1, sc.aux));
+            CU(cudaEventRecord(sc.ev_join, sc.aux));
+            CU(cudaStreamWaitEvent(s, sc.ev_join, 0));
         }
     } else {
         CU(launch(kc.fn, threads, smem, kc.L, 0u, total, counters, s));
@@ -475,8 +530,11 @@ bool choose_peripheral_kernel(const lassim_handle *h, KernelChoice *out) {
     return false;
 }
 
-int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
+// `sc` = the scratch this evaluation writes to; `main` evaluations (the entry points) are
+// the ones the handle's timing events and lassim_last_* diagnostics refer to.
+int launch_eval(lassim_handle *h, Scratch &sc, int N, int mode, const double *dX, double *dY,
                 cudaStream_t s, const int *d_pgene = nullptr) {
+    const bool is_main = &sc == &h->main;
     const bool periph = d_pgene != nullptr;
     KernelChoice kc;
     if (periph) {
@@ -489,19 +547,19 @@ int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
     }
     const int K = periph ? 1 : h->K, n = periph ? h->n + 1 : h->n;
     const ZeroLayout z = zero_layout(N);
-    CU(h->d_zero.reserve(z.bytes));
-    CU(h->d_cost.reserve(N));
-    CU(h->d_cost_main.reserve(N));
-    CU(h->d_pert_cost.reserve(N));
-    CU(h->d_steps.reserve((size_t)N * K));
-    CU(h->d_long.reserve((size_t)N));
+    CU(sc.zero.reserve(z.bytes));
+    CU(sc.cost.reserve(N));
+    CU(sc.cost_main.reserve(N));
+    CU(sc.pert_cost.reserve(N));
+    CU(sc.steps.reserve((size_t)N * K));
+    CU(sc.long_list.reserve((size_t)N));
     if (!dY) {
-        CU(h->d_Y.reserve((size_t)N * h->T * n));
-        dY = h->d_Y.p;
+        CU(sc.Y.reserve((size_t)N * h->T * n));
+        dY = sc.Y.p;
     }
-    if (K > 1 && mode == 0) CU(h->d_E.reserve((size_t)N * K * n));
-    CU(cudaMemsetAsync(h->d_zero.p, 0, z.bytes, s));
-    CU(cudaMemsetAsync(h->d_steps.p, 0, sizeof(unsigned) * (size_t)N * K, s));
+    if (K > 1 && mode == 0) CU(sc.E.reserve((size_t)N * K * n));
+    CU(cudaMemsetAsync(sc.zero.p, 0, z.bytes, s));
+    CU(cudaMemsetAsync(sc.steps.p, 0, sizeof(unsigned) * (size_t)N * K, s));
 
     DevProblem P;
     P.n = n; P.T = h->T; P.K = K; P.U = h->U; P.dim = h->dim; P.nnz = h->nnz;
@@ -520,30 +578,41 @@ int launch_eval(lassim_handle *h, int N, int mode, const double *dX, double *dY,
     DevBatch B;
     B.N = N; B.mode = mode; B.X = dX; B.pgene = d_pgene;
     B.work_begin = 0; B.work_count = 0;     // set per launch below
-    B.cost = h->d_cost.p; B.cost_main = h->d_cost_main.p; B.pert_cost = h->d_pert_cost.p;
-    B.work_counter = reinterpret_cast<unsigned int *>(h->d_zero.p);
-    B.done = reinterpret_cast<int *>(h->d_zero.p + z.off_done);
-    B.status = reinterpret_cast<int *>(h->d_zero.p + z.off_status);
-    B.counters = reinterpret_cast<unsigned long long *>(h->d_zero.p + z.off_counters);
-    B.Y = dY; B.E = h->d_E.p; B.traj_steps = h->d_steps.p; B.order = nullptr;
-    B.long_list = h->d_long.p;
+    B.cost = sc.cost.p; B.cost_main = sc.cost_main.p; B.pert_cost = sc.pert_cost.p;
+    B.work_counter = reinterpret_cast<unsigned int *>(sc.zero.p);
+    B.done = reinterpret_cast<int *>(sc.zero.p + z.off_done);
+    B.status = reinterpret_cast<int *>(sc.zero.p + z.off_status);
+    B.counters = reinterpret_cast<unsigned long long *>(sc.zero.p + z.off_counters);
+    B.Y = dY; B.E = sc.E.p; B.traj_steps = sc.steps.p; B.order = nullptr;
+    B.long_list = sc.long_list.p;
 
-    CU(cudaEventRecord(h->ev0, s));
+    if (is_main) CU(cudaEventRecord(h->ev0, s));
     int rc = launch_kernels(h, kc, P, B, N, mode == 0 ? K : 1, periph, s,
-                            reinterpret_cast<unsigned int *>(h->d_zero.p));
+                            reinterpret_cast<unsigned int *>(sc.zero.p), sc, is_main);
     if (rc) return rc;
-    CU(cudaEventRecord(h->ev1, s));
-    h->timed = true;
-    h->last_N = N;
-    h->last_had_E = (K > 1 && mode == 0);
+    if (is_main) {
+        CU(cudaEventRecord(h->ev1, s));
+        h->timed = true;
+        h->last_N = N;
+        h->last_had_E = (K > 1 && mode == 0);
+    }
     return LASSIM_OK;
+}
+
+void release_de_lanes(lassim_handle *h) {
+    for (DeLane &lane : h->de_lanes) {
+        lane.scratch.release();
+        if (lane.ev_done) cudaEventDestroy(lane.ev_done);
+        if (lane.stream) cudaStreamDestroy(lane.stream);
+    }
+    h->de_lanes.clear();
 }
 
 }  // namespace
 
 extern "C" {
 
-const char *lassim_version(void) { return "0.1.0"; }
+const char *lassim_version(void) { return "0.2.0"; }
 
 const char *lassim_last_error(const lassim_handle *h) {
     return h ? h->err.c_str() : g_create_error.c_str();
@@ -576,20 +645,22 @@ int lassim_create(int device, lassim_handle **out) {
     h->sm_count = prop.multiProcessorCount;
     // the auxiliary stream carries the short trajectories of a speculative evaluation:
     // lowest priority, so that the time series' blocks are placed first
-    int prio_lo = 0, prio_hi = 0;
-    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
-    if (cudaStreamCreateWithPriority(&h->stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
-        cudaStreamCreateWithPriority(&h->stream2, cudaStreamNonBlocking, prio_lo) != cudaSuccess ||
+    cudaDeviceGetStreamPriorityRange(&h->prio_lo, &h->prio_hi);
+    if (cudaStreamCreateWithPriority(&h->stream, cudaStreamNonBlocking, h->prio_hi) != cudaSuccess ||
+        h->main.init(h->prio_lo) != cudaSuccess ||
         cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess ||
         cudaEventCreate(&h->ev_sp0) != cudaSuccess || cudaEventCreate(&h->ev_sp1) != cudaSuccess ||
-        cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+        cudaEventCreateWithFlags(&h->ev_de_fork, cudaEventDisableTiming) != cudaSuccess) {
         delete h;
         return fail(nullptr, LASSIM_E_CUDA, "stream/event creation failed");
     }
     if (const char *sp = getenv("LASSIM_SPECULATE")) h->speculate = atoi(sp);
     if (const char *sp = getenv("LASSIM_SERIES_CAP")) h->series_cap = (unsigned)atoi(sp);
     if (const char *sp = getenv("LASSIM_HANDOVER_WARPS")) h->handover_warps = atoi(sp);
+    if (const char *sp = getenv("LASSIM_HANDOVER_MIN")) h->ho_min = (unsigned)atoi(sp);
+    if (const char *sp = getenv("LASSIM_HANDOVER_MAX")) h->ho_max = (unsigned)atoi(sp);
+    if (const char *sp = getenv("LASSIM_HANDOVER_REMAINING")) h->ho_rem = atof(sp);
+    if (const char *sp = getenv("LASSIM_DE_LANES")) h->de_lanes_wanted = atoi(sp);
     double tab[kExpTable];
     for (int j = 0; j < kExpTable; ++j) tab[j] = exp2((double)j / (double)kExpTable);
     if (cudaMemcpyToSymbol(c_exp2_table, tab, sizeof(tab)) != cudaSuccess) {
@@ -603,8 +674,7 @@ int lassim_create(int device, lassim_handle **out) {
 int lassim_destroy(lassim_handle *h) {
     if (!h) return LASSIM_OK;
     DeviceGuard guard_(h->device);
-    cudaStreamSynchronize(h->stream);
-    cudaStreamSynchronize(h->stream2);
+    cudaDeviceSynchronize();
     h->d_times.release(); h->d_y0.release(); h->d_data.release(); h->d_sigma2.release();
     h->d_pert.release(); h->d_traj_tt.release(); h->d_kidx.release();
     h->d_row_ptr.release(); h->d_col_idx.release();
@@ -613,13 +683,12 @@ int lassim_destroy(lassim_handle *h) {
     h->de_X.release(); h->de_F.release(); h->de_trial.release(); h->de_best.release();
     h->de_table.release(); h->de_lb.release(); h->de_ub.release();
     h->d_traj_prefix.release(); h->d_knock_ctrl.release();
-    h->d_X.release(); h->d_cost.release(); h->d_cost_main.release();
-    h->d_pert_cost.release(); h->d_Y.release(); h->d_E.release(); h->d_probe.release();
-    h->d_zero.release(); h->d_steps.release(); h->d_long.release();
+    h->d_X.release(); h->d_probe.release();
+    h->main.release();
+    release_de_lanes(h);
     cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
-    cudaEventDestroy(h->ev_fork); cudaEventDestroy(h->ev_join);
     cudaEventDestroy(h->ev_sp0); cudaEventDestroy(h->ev_sp1);
-    cudaStreamDestroy(h->stream2);
+    if (h->ev_de_fork) cudaEventDestroy(h->ev_de_fork);
     cudaStreamDestroy(h->stream);
     delete h;
     return LASSIM_OK;
@@ -710,6 +779,10 @@ int lassim_set_mask(lassim_handle *h, const unsigned char *mask) {
     if (!mask) return fail(h, LASSIM_E_INVALID, "mask is NULL");
     DeviceGuard guard_(h->device);
     CU(guard_.err);
+    // the peripheral set-up and the device populations were laid out for the old mask
+    // (core_x is indexed through kidx, the populations have the old dimension)
+    h->p_genes = 0;
+    h->de_ready = false;
     return upload_mask(h, mask);
 }
 
@@ -728,12 +801,23 @@ int lassim_set_series_cap(lassim_handle *h, unsigned int attempts) {
     return LASSIM_OK;
 }
 
+int lassim_set_handover_rule(lassim_handle *h, unsigned int min_attempts, double remaining_steps,
+                             unsigned int max_attempts) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!(remaining_steps >= 0.0) || max_attempts < 1u)
+        return fail(h, LASSIM_E_INVALID, "set_handover_rule: min %u, remaining %g, max %u",
+                    min_attempts, remaining_steps, max_attempts);
+    h->ho_min = min_attempts; h->ho_rem = remaining_steps; h->ho_max = max_attempts;
+    return LASSIM_OK;
+}
+
 int lassim_set_speculation(lassim_handle *h, int mode) {
     if (!h) return LASSIM_E_INVALID;
     if (mode < 0 || mode > 6)
         return fail(h, LASSIM_E_INVALID,
                     "time-series kernel mode %d (0 standard, 1 speculative, 2 auto, 3 stage-parallel, "
-                    "4 stage-parallel + speculative)", mode);
+                    "4 stage-parallel with two step sizes, 5 hand-over, 6 stage-parallel with three "
+                    "step sizes)", mode);
     h->speculate = mode;
     return LASSIM_OK;
 }
@@ -782,11 +866,11 @@ long long lassim_series_flops_per_attempt(const lassim_handle *h, int N) {
 
 int lassim_last_stage_parallel_attempts(lassim_handle *h, unsigned long long *attempts) {
     if (!h || !attempts) return LASSIM_E_INVALID;
-    if (!h->timed || !h->d_zero.p) return fail(h, LASSIM_E_STATE, "no evaluation has run yet");
+    if (!h->timed || !h->main.zero.p) return fail(h, LASSIM_E_STATE, "no evaluation has run yet");
     DeviceGuard guard_(h->device);
     CU(guard_.err);
     CU(cudaDeviceSynchronize());
-    CU(cudaMemcpy(attempts, h->d_zero.p + 16, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(attempts, h->main.zero.p + 16, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     return LASSIM_OK;
 }
 
@@ -843,16 +927,16 @@ int lassim_eval_device(lassim_handle *h, int N, const double *dX, double *dcost,
     DeviceGuard guard_(h->device);
     CU(guard_.err);
     cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
-    int rc = launch_eval(h, N, 0, dX, nullptr, s);
+    int rc = launch_eval(h, h->main, N, 0, dX, nullptr, s);
     if (rc) return rc;
     const ZeroLayout z = zero_layout(N);
     const size_t nb = sizeof(double) * (size_t)N;
-    CU(cudaMemcpyAsync(dcost, h->d_cost.p, nb, cudaMemcpyDeviceToDevice, s));
-    if (dcost_main) CU(cudaMemcpyAsync(dcost_main, h->d_cost_main.p, nb, cudaMemcpyDeviceToDevice, s));
-    if (dpert_cost) CU(cudaMemcpyAsync(dpert_cost, h->d_pert_cost.p, nb, cudaMemcpyDeviceToDevice, s));
-    if (dstatus) CU(cudaMemcpyAsync(dstatus, h->d_zero.p + z.off_status, sizeof(int) * (size_t)N,
+    CU(cudaMemcpyAsync(dcost, h->main.cost.p, nb, cudaMemcpyDeviceToDevice, s));
+    if (dcost_main) CU(cudaMemcpyAsync(dcost_main, h->main.cost_main.p, nb, cudaMemcpyDeviceToDevice, s));
+    if (dpert_cost) CU(cudaMemcpyAsync(dpert_cost, h->main.pert_cost.p, nb, cudaMemcpyDeviceToDevice, s));
+    if (dstatus) CU(cudaMemcpyAsync(dstatus, h->main.zero.p + z.off_status, sizeof(int) * (size_t)N,
                                     cudaMemcpyDeviceToDevice, s));
-    if (dcounters) CU(cudaMemcpyAsync(dcounters, h->d_zero.p + z.off_counters,
+    if (dcounters) CU(cudaMemcpyAsync(dcounters, h->main.zero.p + z.off_counters,
                                       sizeof(unsigned long long) * 3 * (size_t)N,
                                       cudaMemcpyDeviceToDevice, s));
     return LASSIM_OK;
@@ -872,16 +956,16 @@ int lassim_eval(lassim_handle *h, int N, const double *X, double *cost,
     CU(h->d_X.reserve((size_t)N * h->dim));
     CU(cudaMemcpyAsync(h->d_X.p, X, sizeof(double) * (size_t)N * h->dim,
                        cudaMemcpyHostToDevice, s));
-    int rc = launch_eval(h, N, 0, h->d_X.p, nullptr, s);
+    int rc = launch_eval(h, h->main, N, 0, h->d_X.p, nullptr, s);
     if (rc) return rc;
     const ZeroLayout z = zero_layout(N);
     const size_t nb = sizeof(double) * (size_t)N;
-    CU(cudaMemcpyAsync(cost, h->d_cost.p, nb, cudaMemcpyDeviceToHost, s));
-    if (cost_main) CU(cudaMemcpyAsync(cost_main, h->d_cost_main.p, nb, cudaMemcpyDeviceToHost, s));
-    if (pert_cost) CU(cudaMemcpyAsync(pert_cost, h->d_pert_cost.p, nb, cudaMemcpyDeviceToHost, s));
-    if (status) CU(cudaMemcpyAsync(status, h->d_zero.p + z.off_status, sizeof(int) * (size_t)N,
+    CU(cudaMemcpyAsync(cost, h->main.cost.p, nb, cudaMemcpyDeviceToHost, s));
+    if (cost_main) CU(cudaMemcpyAsync(cost_main, h->main.cost_main.p, nb, cudaMemcpyDeviceToHost, s));
+    if (pert_cost) CU(cudaMemcpyAsync(pert_cost, h->main.pert_cost.p, nb, cudaMemcpyDeviceToHost, s));
+    if (status) CU(cudaMemcpyAsync(status, h->main.zero.p + z.off_status, sizeof(int) * (size_t)N,
                                    cudaMemcpyDeviceToHost, s));
-    if (counters) CU(cudaMemcpyAsync(counters, h->d_zero.p + z.off_counters,
+    if (counters) CU(cudaMemcpyAsync(counters, h->main.zero.p + z.off_counters,
                                      sizeof(unsigned long long) * 3 * (size_t)N,
                                      cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
@@ -900,12 +984,12 @@ int lassim_trajectories(lassim_handle *h, int N, const double *X, double *Y, int
     CU(h->d_X.reserve((size_t)N * h->dim));
     CU(cudaMemcpyAsync(h->d_X.p, X, sizeof(double) * (size_t)N * h->dim,
                        cudaMemcpyHostToDevice, s));
-    int rc = launch_eval(h, N, 1, h->d_X.p, nullptr, s);
+    int rc = launch_eval(h, h->main, N, 1, h->d_X.p, nullptr, s);
     if (rc) return rc;
     const ZeroLayout z = zero_layout(N);
-    CU(cudaMemcpyAsync(Y, h->d_Y.p, sizeof(double) * (size_t)N * h->T * h->n,
+    CU(cudaMemcpyAsync(Y, h->main.Y.p, sizeof(double) * (size_t)N * h->T * h->n,
                        cudaMemcpyDeviceToHost, s));
-    if (status) CU(cudaMemcpyAsync(status, h->d_zero.p + z.off_status, sizeof(int) * (size_t)N,
+    if (status) CU(cudaMemcpyAsync(status, h->main.zero.p + z.off_status, sizeof(int) * (size_t)N,
                                    cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
     return LASSIM_OK;
@@ -959,11 +1043,11 @@ int lassim_eval_peripheral(lassim_handle *h, int N, const int *gene, const doubl
     CU(h->d_pgene.reserve((size_t)N));
     CU(cudaMemcpyAsync(h->d_X.p, Xp, sizeof(double) * (size_t)N * pdim, cudaMemcpyHostToDevice, s));
     CU(cudaMemcpyAsync(h->d_pgene.p, gene, sizeof(int) * (size_t)N, cudaMemcpyHostToDevice, s));
-    int rc = launch_eval(h, N, 0, h->d_X.p, nullptr, s, h->d_pgene.p);
+    int rc = launch_eval(h, h->main, N, 0, h->d_X.p, nullptr, s, h->d_pgene.p);
     if (rc) return rc;
     const ZeroLayout z = zero_layout(N);
-    CU(cudaMemcpyAsync(cost, h->d_cost.p, sizeof(double) * (size_t)N, cudaMemcpyDeviceToHost, s));
-    if (status) CU(cudaMemcpyAsync(status, h->d_zero.p + z.off_status, sizeof(int) * (size_t)N,
+    CU(cudaMemcpyAsync(cost, h->main.cost.p, sizeof(double) * (size_t)N, cudaMemcpyDeviceToHost, s));
+    if (status) CU(cudaMemcpyAsync(status, h->main.zero.p + z.off_status, sizeof(int) * (size_t)N,
                                    cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
     return LASSIM_OK;
@@ -978,7 +1062,7 @@ int lassim_peripheral_trajectories(lassim_handle *h, int N, const int *gene, con
     if (rc || N == 0) return rc;
     DeviceGuard guard_(h->device);
     CU(guard_.err);
-    CU(cudaMemcpy(Y, h->d_Y.p, sizeof(double) * (size_t)N * h->T * (h->n + 1),
+    CU(cudaMemcpy(Y, h->main.Y.p, sizeof(double) * (size_t)N * h->T * (h->n + 1),
                   cudaMemcpyDeviceToHost));
     return LASSIM_OK;
 }
@@ -990,7 +1074,7 @@ int lassim_last_end_states(lassim_handle *h, int N, double *E) {
     DeviceGuard guard_(h->device);
     CU(guard_.err);
     CU(cudaDeviceSynchronize());
-    CU(cudaMemcpy(E, h->d_E.p, sizeof(double) * (size_t)N * h->K * h->n, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(E, h->main.E.p, sizeof(double) * (size_t)N * h->K * h->n, cudaMemcpyDeviceToHost));
     return LASSIM_OK;
 }
 
@@ -1001,7 +1085,7 @@ int lassim_last_traj_steps(lassim_handle *h, int N, unsigned int *steps) {
     DeviceGuard guard_(h->device);
     CU(guard_.err);
     CU(cudaDeviceSynchronize());
-    CU(cudaMemcpy(steps, h->d_steps.p, sizeof(unsigned) * (size_t)N * h->K, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(steps, h->main.steps.p, sizeof(unsigned) * (size_t)N * h->K, cudaMemcpyDeviceToHost));
     return LASSIM_OK;
 }
 
@@ -1070,17 +1154,36 @@ namespace {
 int de_evaluate_population(lassim_handle *h) {
     const int count = h->de.islands * h->de.np;
     cudaStream_t s = h->stream;
-    int rc = launch_eval(h, count, 0, h->de_X.p, nullptr, s);
+    int rc = launch_eval(h, h->main, count, 0, h->de_X.p, nullptr, s);
     if (rc) return rc;
     const ZeroLayout z = zero_layout(count);
     de_mask_status_kernel<<<(count + 255) / 256, 256, 0, s>>>(
-        count, reinterpret_cast<const int *>(h->d_zero.p + z.off_status), h->d_cost.p);
+        count, reinterpret_cast<const int *>(h->main.zero.p + z.off_status), h->main.cost.p);
     CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(h->de_F.p, h->d_cost.p, sizeof(double) * (size_t)count,
+    CU(cudaMemcpyAsync(h->de_F.p, h->main.cost.p, sizeof(double) * (size_t)count,
                        cudaMemcpyDeviceToDevice, s));
     h->launches += 1;
     h->de_evaluations += count;
     h->de_evaluated = true;
+    return LASSIM_OK;
+}
+
+// Lanes of the asynchronous evolve: `lanes` groups of consecutive islands, each with its own
+// stream and evaluation scratch.  Automatic: one island per lane up to 16 lanes.
+int de_make_lanes(lassim_handle *h) {
+    release_de_lanes(h);
+    const int islands = h->de.islands;
+    int lanes = h->de_lanes_wanted > 0 ? h->de_lanes_wanted : (islands < 16 ? islands : 16);
+    if (lanes > islands) lanes = islands;
+    h->de_lanes.resize(lanes);
+    for (int l = 0; l < lanes; ++l) {
+        DeLane &lane = h->de_lanes[l];
+        lane.first = (int)((long long)islands * l / lanes);
+        lane.count = (int)((long long)islands * (l + 1) / lanes) - lane.first;
+        CU(cudaStreamCreateWithPriority(&lane.stream, cudaStreamNonBlocking, h->prio_hi));
+        CU(cudaEventCreateWithFlags(&lane.ev_done, cudaEventDisableTiming));
+        CU(lane.scratch.init(h->prio_lo));
+    }
     return LASSIM_OK;
 }
 
@@ -1099,6 +1202,7 @@ extern "C" int lassim_de_init(lassim_handle *h, int islands, int individuals, in
     DeviceGuard guard_(h->device);
     CU(guard_.err);
     const size_t dim = (size_t)h->dim, count = (size_t)islands * individuals;
+    CU(cudaStreamSynchronize(h->stream));        // nothing of a previous run is in flight
     CU(h->de_X.reserve(count * dim));
     CU(h->de_trial.reserve(count * dim));
     CU(h->de_F.reserve(count));
@@ -1110,9 +1214,36 @@ extern "C" int lassim_de_init(lassim_handle *h, int islands, int individuals, in
                        h->stream));
     CU(cudaStreamSynchronize(h->stream));
     h->de = DeParams{islands, individuals, (int)dim, variant, f, cr, seed, 0ull};
+    h->de.gid_base = 0; h->de.gid_stride = 1;
+    h->de.ind_begin = 0; h->de.ind_end = (int)count;
+    if ((rc = de_make_lanes(h))) return rc;
     h->de_ready = true;
     h->de_evaluated = false;
     h->de_evaluations = 0;
+    return LASSIM_OK;
+}
+
+extern "C" int lassim_de_set_island_ids(lassim_handle *h, int first_island, int stride) {
+    if (!h) return LASSIM_E_INVALID;
+    if (!h->de_ready) return fail(h, LASSIM_E_STATE, "de_set_island_ids before de_init");
+    if (first_island < 0 || stride < 1)
+        return fail(h, LASSIM_E_INVALID, "de_set_island_ids: first island %d, stride %d",
+                    first_island, stride);
+    h->de.gid_base = first_island;
+    h->de.gid_stride = stride;
+    return LASSIM_OK;
+}
+
+extern "C" int lassim_de_set_lanes(lassim_handle *h, int lanes) {
+    if (!h) return LASSIM_E_INVALID;
+    if (lanes < 0) return fail(h, LASSIM_E_INVALID, "de_set_lanes: lanes=%d", lanes);
+    h->de_lanes_wanted = lanes;
+    if (h->de_ready) {
+        DeviceGuard guard_(h->device);
+        CU(guard_.err);
+        CU(cudaDeviceSynchronize());
+        return de_make_lanes(h);
+    }
     return LASSIM_OK;
 }
 
@@ -1130,6 +1261,15 @@ extern "C" int lassim_de_set_individual(lassim_handle *h, int island, int index,
     return LASSIM_OK;
 }
 
+// One evolve round.  Islands do not wait for each other inside a round (PyGMO evolves every
+// island in a worker of its own and joins them at the end,
+// source/core/base_optimization.py:173-174): each lane - a group of islands - runs its
+// `generations` x (trial vectors -> evaluation -> selection) on its own stream with its own
+// scratch, so one island's slow candidate holds up that island's next generation only while
+// the other islands' kernels fill the machine.  The lanes fork from the handle's stream and
+// join it again at the end (migration and the getters follow on that stream).  A
+// candidate's cost does not depend on the batch it is evaluated in, so the lanes change
+// the schedule, not the result.
 extern "C" int lassim_de_evolve(lassim_handle *h, int generations) {
     if (!h) return LASSIM_E_INVALID;
     if (!h->de_ready) return fail(h, LASSIM_E_STATE, "de_evolve before de_init");
@@ -1139,25 +1279,40 @@ extern "C" int lassim_de_evolve(lassim_handle *h, int generations) {
     if (generations < 0) return fail(h, LASSIM_E_INVALID, "de_evolve: generations=%d", generations);
     DeviceGuard guard_(h->device);
     CU(guard_.err);
-    cudaStream_t s = h->stream;
-    const int count = h->de.islands * h->de.np;
-    const int blocks = (count + 127) / 128;
     int rc;
     if (!h->de_evaluated && (rc = de_evaluate_population(h))) return rc;
+    if (generations == 0) return LASSIM_OK;
+    CU(cudaEventRecord(h->ev_de_fork, h->stream));
+    for (DeLane &lane : h->de_lanes) CU(cudaStreamWaitEvent(lane.stream, h->ev_de_fork, 0));
+    const int np = h->de.np, dim = h->de.dim;
     for (int g = 0; g < generations; ++g) {
-        de_trial_kernel<<<blocks, 128, 0, s>>>(h->de, h->de_X.p, h->de_F.p, h->de_lb.p,
-                                                h->de_ub.p, h->de_trial.p);
-        CU(cudaGetLastError());
-        if ((rc = launch_eval(h, count, 0, h->de_trial.p, nullptr, s))) return rc;
-        const ZeroLayout z = zero_layout(count);
-        de_mask_status_kernel<<<(count + 255) / 256, 256, 0, s>>>(
-            count, reinterpret_cast<const int *>(h->d_zero.p + z.off_status), h->d_cost.p);
-        de_select_kernel<<<blocks, 128, 0, s>>>(h->de, h->de_X.p, h->de_F.p, h->de_trial.p,
-                                                 h->d_cost.p);
-        CU(cudaGetLastError());
-        h->launches += 3;
+        for (DeLane &lane : h->de_lanes) {
+            cudaStream_t s = lane.stream;
+            const int count = lane.count * np;
+            DeParams p = h->de;
+            p.ind_begin = lane.first * np;
+            p.ind_end = p.ind_begin + count;
+            const int blocks = (count + 127) / 128;
+            de_trial_kernel<<<blocks, 128, 0, s>>>(p, h->de_X.p, h->de_F.p, h->de_lb.p,
+                                                    h->de_ub.p, h->de_trial.p);
+            CU(cudaGetLastError());
+            const double *trial = h->de_trial.p + (size_t)p.ind_begin * dim;
+            if ((rc = launch_eval(h, lane.scratch, count, 0, trial, nullptr, s))) return rc;
+            const ZeroLayout z = zero_layout(count);
+            de_mask_status_kernel<<<(count + 255) / 256, 256, 0, s>>>(
+                count, reinterpret_cast<const int *>(lane.scratch.zero.p + z.off_status),
+                lane.scratch.cost.p);
+            de_select_kernel<<<blocks, 128, 0, s>>>(p, h->de_X.p, h->de_F.p, h->de_trial.p,
+                                                     lane.scratch.cost.p);
+            CU(cudaGetLastError());
+            h->launches += 3;
+            h->de_evaluations += count;
+        }
         h->de.generation += 1;
-        h->de_evaluations += count;
+    }
+    for (DeLane &lane : h->de_lanes) {
+        CU(cudaEventRecord(lane.ev_done, lane.stream));
+        CU(cudaStreamWaitEvent(h->stream, lane.ev_done, 0));
     }
     return LASSIM_OK;       // enqueued; lassim_de_get / lassim_de_best synchronise
 }
@@ -1341,7 +1496,8 @@ extern "C" int lassim_eval_device_noalloc(lassim_handle *h, int N, const double 
     B.long_list = reinterpret_cast<unsigned long long *>(base + L.off_long);
 
     // same kernels, same speculation policy as lassim_eval_device: same costs
-    int rc = launch_kernels(h, kc, P, B, N, K, false, s, reinterpret_cast<unsigned int *>(base));
+    int rc = launch_kernels(h, kc, P, B, N, K, false, s, reinterpret_cast<unsigned int *>(base),
+                            h->main, false);
     if (rc) return rc;
     return LASSIM_OK;
 }

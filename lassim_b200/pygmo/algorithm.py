@@ -78,12 +78,13 @@ class de:
             mutant = partner(4) + F * (partner(0) + partner(1) - partner(2) - partner(3))
         if self.variant <= 5:
             # exponential crossover: a run of consecutive components starting
-            # at a random index, continued while rand < CR (at least one)
+            # at a random index: the first always, then one more for every
+            # draw < CR until the first failure (pagmo's do/while; at most D)
             start = rng.integers(0, D, size=NP)
             u = rng.random((NP, D))
             stop = np.argmax(u >= self.cr, axis=1)
-            length = np.where((u >= self.cr).any(axis=1), stop, D)
-            length = np.maximum(length, 1)
+            length = np.where((u >= self.cr).any(axis=1), 1 + stop, D)
+            length = np.minimum(length, D)
             offs = (np.arange(D)[None, :] - start[:, None]) % D
             cross = offs < length[:, None]
         else:

@@ -66,6 +66,9 @@ class device_archipelago:
         X0 = np.stack([self._islands[i].population.X for i in self._own])
         eng.de_init(X0, prob.lb, prob.ub, variant=algo.variant, f=algo.f, cr=algo.cr,
                     seed=self._seed)
+        # islands are dealt round-robin to ranks: local island j is island own[0] + j * world
+        stride = self._own[1] - self._own[0] if len(self._own) > 1 else 1
+        eng.de_set_island_ids(self._own[0], stride)
         self._engine, self._algo, self._prob = eng, algo, prob
 
     def evolve(self, n=1):

@@ -19,6 +19,9 @@ What it does
 Populations:
   th2_uniform : rows 0..G-1 of default_rng(0).uniform(lb, ub, (1024, 87))
                 (the same X the bench uses at full size)
+  th2_uniform_full : all 1024 rows of that population: the reference's totals and
+                parts, its knock-down ratio vectors and control end states, and the
+                same at rtol = atol = 1e-13 (X itself is not stored: seed + checksum)
   th2_late    : a few DE generations on the time-series cost, then the
                 population jittered by N(0, 0.05*range) (seed 1)
   syn50       : synthetic 50-gene, in-degree 5 problem (default_rng(50))
@@ -26,7 +29,7 @@ Populations:
                 stiff regime; only the time-series part is run through the
                 reference (a full cost is ~200 solves of ~1 s each)
 
-Usage: python oracle/gen_golden.py [--only th2|syn50|syn200] [--procs 8]
+Usage: python oracle/gen_golden.py [--only th2|th2_full|syn50|syn200] [--procs 8]
 """
 import argparse
 import os
@@ -179,6 +182,42 @@ def _eval_oracle(args):
     return c, pc, np.asarray(Y), sim
 
 
+def _eval_full(x):
+    """One candidate of the full-size population: the reference's own total /
+    parts, the knock-down ratio vector and control end states as the reference's
+    own compiled ode plugin produces them (the a4 loop restated around it; the
+    compiled a4 returns only the scalar, which must come out the same), and the
+    same at rtol = atol = 1e-13."""
+    p, n = _W["prob"], _W["n"]
+    total, cmain, pc, _ = _eval_reference(x)
+
+    def ref_ode(y0, t, sol, k_map, k_mask, size, result):
+        # the compiled plugin scatters into k_map in place: hand it a copy
+        return _W["ode"](y0, t, sol, np.array(k_map, dtype=np.float64).copy(), k_mask, size, result)
+
+    pc2, sim, ctrl = orc.perturbation_cost(p["pert"], n, p["y0"], np.array(x), p["vector_map"],
+                                           p["mask"], ref_ode, return_controls=True)
+    tode = orc.tight_ode()
+    tcm = orc.core_cost(x, p["data"], p["sigma"], p["times"], p["y0"], p["vector_map"],
+                        p["mask"], tode)
+    tpc, tsim, tctrl = orc.perturbation_cost(p["pert"], n, p["y0"], np.array(x), p["vector_map"],
+                                             p["mask"], tode, return_controls=True)
+    return (total, cmain, pc, pc2, sim, ctrl, tcm, tpc, tsim, tctrl)
+
+
+def run_full_population(prob, X, procs, factor=0.5):
+    with Pool(procs, initializer=_worker_init, initargs=(prob, factor)) as pool:
+        rows = pool.map(_eval_full, list(X), chunksize=1)
+    col = lambda i: np.array([r[i] for r in rows])
+    return dict(
+        seed=np.int64(0), rows=np.int64(len(X)), x_checksum=np.float64(X.sum()),
+        pert_factor=np.float64(factor),
+        ref_total=col(0), ref_cost_main=col(1), ref_pert_cost=col(2),
+        ref_pert_cost_from_sim=col(3), ref_sim=col(4), ref_ctrl_end=col(5),
+        tight_cost_main=col(6), tight_pert_cost=col(7), tight_sim=col(8),
+        tight_ctrl_end=col(9))
+
+
 def _lsoda_stats(x):
     p = _W["prob"]
     _, info = orc.odeint_lassim(p["y0"], p["times"], np.array(x),
@@ -274,6 +313,15 @@ def main():
         out = run_population(prob, Xl, a.procs)
         np.savez_compressed(os.path.join(GOLD, "th2_late.npz"), **out)
         print("th2_late: ref totals", out["ref_total"][:4])
+
+    if a.only in ("all", "th2_full"):
+        # every row of the population bench.py times (config 2), so that the bench line and
+        # the parity tests can be checked against the reference on all 1024 of them
+        prob = load_th2_with_reference()
+        X = synth.uniform_population(prob["lb"], prob["ub"], 1024, seed=0)
+        out = run_full_population(prob, X, a.procs)
+        np.savez_compressed(os.path.join(GOLD, "th2_uniform_full.npz"), **out)
+        print("th2_uniform_full: ref totals", out["ref_total"][:4])
 
     if a.only in ("all", "syn50"):
         prob = synth.synthetic_problem(50, seed=50)

@@ -95,7 +95,7 @@ def rank1_residual(sim, p):
 
 
 def perturbation_cost(pert_data, size, y0, sol_vector, vector_map, mask,
-                      ode=odeint_lassim, return_sim=False):
+                      ode=odeint_lassim, return_sim=False, return_controls=False):
     """a4: cumulative knock-downs (perturbation_functions.pyx:64-85): at row i
     the control for a new (t_start, t_end) pair is solved with the lambdas as
     scaled so far, then lambda_i *= P[i,i] (never undone), then the knocked
@@ -121,6 +121,9 @@ def perturbation_cost(pert_data, size, y0, sol_vector, vector_map, mask,
         sim -= 1.0
         sim[sim > 2] = 2
         cost = rank1_residual(sim, perts.flatten())
+    if return_controls:
+        # control end states in order of first appearance of their time pair
+        return cost, sim, np.array([c[-1] for c in controls.values()])
     if return_sim:
         return cost, sim
     return cost

@@ -166,3 +166,25 @@ def test_peripheral_genes_shard_by_rank(tmp_path):
     g0 = np.load(tmp_path / "genes_0.npy")
     g1 = np.load(tmp_path / "genes_1.npy")
     assert g0.tolist() == [0, 2, 4, 6, 8, 10] and g1.tolist() == [1, 3, 5, 7, 9]
+
+
+def test_exponential_crossover_length_is_pagmos():
+    """pagmo's do/while copies the first component always, then one more for every draw below
+    CR until the first failure: length = 1 + Geometric, capped at the dimension (the device
+    kernel, de_trial_kernel, does the same)."""
+    D, NP, cr = 12, 4000, 0.6
+    prob = Sphere(D)
+    algo = algorithm.de(gen=1, f=0.5, cr=cr, variant=2)
+    isl = island(algo, prob, NP, seed=5)
+    X = isl.population.X
+    X[:] = np.random.default_rng(1).uniform(-4, 4, X.shape)       # mutants differ everywhere
+    trial = algo.propose(isl.population)
+    length = (trial != X).sum(axis=1)
+    assert length.min() == 1 and length.max() == D
+    want = np.array([cr ** (k - 1) * (1 - cr) for k in range(1, D)] + [cr ** (D - 1)])
+    got = np.bincount(length, minlength=D + 1)[1:] / NP
+    assert np.abs(got - want).max() < 0.03
+    # the run is contiguous modulo D
+    changed = trial != X
+    starts = (changed & ~np.roll(changed, 1, axis=1)).sum(axis=1)
+    assert ((starts == 1) | (length == D)).all()

@@ -73,3 +73,51 @@ def test_device_de_improves_like_the_host_driver(th2):
     assert fd < f0 and fh < f0
     # same algorithm, different random streams: the same order of improvement
     assert fd < f0 - 0.3 * (f0 - fh)
+
+
+def test_islands_evolve_concurrently_with_the_same_result(th2):
+    """Inside an evolve round every lane (group of islands) runs its generations on a stream
+    of its own (lassim_de_set_lanes; PyGMO's islands do not wait for each other either,
+    base_optimization.py:173-174).  A candidate's cost does not depend on the batch it is
+    evaluated in, so 1 lane (lockstep), 2 and one lane per island give the same populations."""
+    from lassim_b200 import Engine
+    p = th2
+    rng = np.random.default_rng(11)
+    X0 = rng.uniform(p["lb"], p["ub"], size=(5, 16, 87))
+    results = []
+    for lanes in (1, 2, 0):
+        eng = Engine(0)
+        eng.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"], p["pert"], 0.5)
+        eng.de_init(X0, p["lb"], p["ub"], variant=3, f=0.85, cr=1.0, seed=9)
+        eng.de_set_island_ids(3, 2)
+        eng.de_set_lanes(lanes)
+        eng.de_evolve(4)
+        table = eng.de_best()
+        eng.de_migrate_ring(np.tile(table, (3, 1))[:13], 3, 2)
+        eng.de_evolve(2)
+        results.append(eng.de_get())
+        assert eng.de_evaluations == 5 * 16 * 7
+        eng.close()
+    for X, F in results[1:]:
+        np.testing.assert_array_equal(X, results[0][0])
+        np.testing.assert_array_equal(F, results[0][1])
+    assert (results[0][1] <= np.inf).all() and np.isfinite(results[0][1]).mean() > 0.9
+
+
+def test_islands_on_different_gpus_draw_different_numbers(th2):
+    """The random streams are keyed by the island's position in the whole archipelago, not
+    by its slot on this GPU: two GPUs given the same seed must not propose the same trials."""
+    from lassim_b200 import Engine
+    p = th2
+    X0 = np.random.default_rng(2).uniform(p["lb"], p["ub"], size=(1, 8, 87))
+    pops = []
+    for first in (0, 1, 0):
+        eng = Engine(0)
+        eng.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"], None, 0.0)
+        eng.de_init(X0, p["lb"], p["ub"], variant=2, f=0.8, cr=0.9, seed=4)
+        eng.de_set_island_ids(first, 2)
+        eng.de_evolve(3)
+        pops.append(eng.de_get()[0])
+        eng.close()
+    np.testing.assert_array_equal(pops[0], pops[2])
+    assert not np.array_equal(pops[0], pops[1])

@@ -141,6 +141,86 @@ def test_knock_down_end_states_and_reduction(engine, th2, th2_uniform):
         assert out["pert_cost"][c] == pytest.approx(orc.rank1_residual(sim, pflat), rel=1e-10)
 
 
+def test_full_population_against_the_reference(engine, th2):
+    """All 1024 rows of the population bench.py times (BASELINE config 2) against what the
+    reference's own code returned for them (tests/golden/th2_uniform_full.npz).
+
+    Gates, as SURVEY.md 8c sets them: relative 1e-6 against the reference on the rows where
+    the reference itself is converged (agrees with the same functions at rtol = atol = 1e-13
+    to 1e-7) - for the time-series cost, for the knock-down cost and for the total, each on
+    its own converged set.  SURVEY's other criterion for the knock-down cost (all control end
+    states above 1e-6) selects nobody in this population: every uniform candidate has a gene
+    that decays to 1e-30 or less by t = 24, so "converged" is the criterion that is left.
+    Elsewhere the knock-down cost is a ratio of integration noise (LSODA's +-1e-18 remnants
+    against true values of 1e-100) in the reference and here alike: reported, not gated."""
+    g = load_golden("th2_uniform_full")
+    p = th2
+    X = np.random.default_rng(int(g["seed"])).uniform(p["lb"], p["ub"], size=(int(g["rows"]), 87))
+    assert X.sum() == float(g["x_checksum"])
+    bind_th2(engine, p, factor=float(g["pert_factor"]))
+    out = engine.eval(X, details=True)
+    assert (out["status"] == 0).all()
+    ref_m, tight_m = g["ref_cost_main"], g["tight_cost_main"]
+    ref_p, tight_p = g["ref_pert_cost"], g["tight_pert_cost"]
+    main_ok = rel(ref_m, tight_m) <= 1e-7
+    pert_ok = rel(ref_p, tight_p) <= 1e-7
+    both = main_ok & pert_ok
+    print("\nconverged sets: time series %d, knock-down %d, both %d of %d"
+          % (main_ok.sum(), pert_ok.sum(), both.sum(), len(X)))
+    assert main_ok.sum() > 900 and pert_ok.sum() > 200
+    assert rel(out["cost_main"], ref_m)[main_ok].max() <= COST_RTOL
+    assert rel(out["cost_main"], tight_m).max() <= 1e-4
+    e_p = rel(out["pert_cost"], ref_p)
+    print("knock-down cost vs reference on its converged set: max %.2e; elsewhere median %.2e "
+          "(reference vs its own converged answer there: median %.2e); non-finite here %d, "
+          "in the reference %d" % (e_p[pert_ok].max(), np.nanmedian(e_p[~pert_ok]),
+                                   np.nanmedian(rel(ref_p, tight_p)[~pert_ok]),
+                                   int((~np.isfinite(out["pert_cost"])).sum()),
+                                   int((~np.isfinite(ref_p)).sum())))
+    assert e_p[pert_ok].max() <= COST_RTOL
+    assert rel(out["cost"], g["ref_total"])[both].max() <= COST_RTOL
+    # the ratio vector behind the knock-down cost, entry by entry, against the reference's own
+    # end states: clipped entries are 2 in both, the others agree where they are not noise
+    # (|control end state| of the tight solve above 1e-6)
+    E = engine.last_end_states(len(X))
+    n = 12
+    sim = np.empty((len(X), n * n))
+    for i in range(n):
+        u = 1 if p["pert"][i, n + 1] == p["pert"][0, n + 1] else 2
+        with np.errstate(all="ignore"):
+            sim[:, i * n:(i + 1) * n] = E[:, 3 + i] / E[:, u]
+    sim -= 1.0
+    sim[sim > 2] = 2
+    ctrl = np.empty((len(X), n * n))
+    for i in range(n):
+        u = 0 if p["pert"][i, n + 1] == p["pert"][0, n + 1] else 1
+        ctrl[:, i * n:(i + 1) * n] = g["tight_ctrl_end"][:, u]
+    solid = (np.abs(ctrl) > 1e-6) & (g["tight_sim"] < 2) & np.isfinite(g["ref_sim"])
+    assert solid.sum() > 10000
+    np.testing.assert_allclose(sim[solid], g["ref_sim"][solid], rtol=1e-5, atol=1e-6)
+
+
+def test_cost_does_not_depend_on_the_batch(engine, th2):
+    """_objfun_impl(x) - a batch of one - and the same x inside a population of 1024 give the
+    same bits (the reference evaluates candidates one by one, core_problem.py:134-155, so a
+    champion's stored cost must equal its re-evaluation): neither the kernel choice nor the
+    hand-over of long time series looks at the batch size.  Rows 415 and 820 are the two
+    limit cycles of this population (12,000 attempts, handed over), 798 a non-finite one."""
+    p = th2
+    bind_th2(engine, p)
+    X = np.random.default_rng(0).uniform(p["lb"], p["ub"], size=(1024, 87))
+    whole = engine.eval(X, details=True)
+    assert engine.last_stage_parallel_attempts() > 0
+    for rows in ([415], [820], [798], [0], list(range(128)), list(range(400, 432)),
+                 [820, 5, 415]):
+        part = engine.eval(X[rows], details=True)
+        for key in ("cost", "cost_main", "pert_cost", "status"):
+            np.testing.assert_array_equal(part[key], whole[key][rows])
+    big = engine.eval(np.concatenate([X] * 3 + [X[:7]]), details=True)      # 3079 candidates
+    np.testing.assert_array_equal(big["cost"][2048:3072], whole["cost"])
+    np.testing.assert_array_equal(big["cost"][3072:], whole["cost"][:7])
+
+
 def mild_population(p, count, seed):
     """Candidates whose states stay O(1): the knock-down cost is then a
     well-conditioned function of the trajectories."""
@@ -535,8 +615,8 @@ def test_time_series_kernels_stay_inside_the_error_control(engine, th2, name):
     (lassim_set_speculation): 'stages' = the stage-parallel Gauss pair, 'stages2' =
     the same with a second warp attempting 0.7 of every step, 'stages3' = three warps
     attempting 1.2, 1 and 0.7 of it, 'handover' = standard kernel first, time series
-    over the attempt cap continue in 'stages3' (what
-    'auto' picks up to 16,384 candidates), 'on' = the explicit pair with a second,
+    picked by the hand-over rule continue in 'stages3' (what
+    'auto' picks), 'on' = the explicit pair with a second,
     shorter attempt in the other half of the warp, 'off' = the standard kernel.  All must pass the parity
     gate, differ from each other only at the level of the integration tolerance,
     and be deterministic."""
@@ -558,7 +638,7 @@ def test_time_series_kernels_stay_inside_the_error_control(engine, th2, name):
         err = np.abs(Y - g["tight_Y"]) / np.maximum(np.abs(g["tight_Y"]), scale)
         assert err[well].max() <= TRAJ_RTOL
         res[mode] = a
-    np.testing.assert_array_equal(res["handover"]["cost"], res["auto"]["cost"])     # N <= 16384
+    np.testing.assert_array_equal(res["handover"]["cost"], res["auto"]["cost"])
     for mode in ("on", "stages", "stages2", "stages3", "handover"):
         assert rel(res[mode]["cost_main"], res["off"]["cost_main"])[well].max() <= COST_RTOL
         # the knock-down trajectories run on the standard kernel either way

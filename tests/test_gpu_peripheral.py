@@ -95,3 +95,26 @@ def test_peripheral_sweep_de(th2):
     one = sweep.problem(5)
     assert one._objfun_impl(tuple(x1[5]))[0] == pytest.approx(f1[5], rel=1e-12)
     assert sweep.evaluate(np.full(genes, 0), hidden)[0] == pytest.approx(0.0, abs=1e-9)
+
+
+def test_a_new_mask_invalidates_the_peripheral_setup(th2):
+    """lassim_set_mask rebuilds the index map the fixed core vector is read through: a
+    peripheral set-up made for the old mask must not be evaluated against the new one
+    (it would read the core's weights through the wrong indices, and out of bounds when
+    the new mask has more edges)."""
+    from lassim_b200 import Engine, LassimError
+    eng = Engine(0)
+    eng.set_problem(th2["data"], th2["sigma"], th2["times"], th2["y0"], th2["mask"], None, 0.0)
+    data, sigma, y0, mask, Xp = peripheral_data(th2, 3)
+    eng.set_peripheral(mild_core(th2), data, sigma, y0, mask)
+    gene = np.arange(3, dtype=np.int32)
+    assert np.isfinite(eng.eval_peripheral(gene, Xp)).all()
+    pruned = th2["mask"].copy()
+    pruned[np.flatnonzero(pruned)[0]] = False
+    eng.set_mask(pruned)
+    with pytest.raises(LassimError, match="set_peripheral"):
+        eng.eval_peripheral(gene, Xp)
+    core = mild_core(th2)
+    eng.set_peripheral(np.delete(core, 24), data, sigma, y0, mask)      # first k entry dropped
+    assert np.isfinite(eng.eval_peripheral(gene, Xp)).all()
+    eng.close()

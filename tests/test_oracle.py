@@ -77,3 +77,27 @@ def test_reference_functions_load_when_built(th2, th2_uniform):
         float(g["pert_factor"]), p["vector_map"], p["mask"], fns)
     assert c == pytest.approx(g["ref_cost_main"][0], rel=1e-13)
     assert tot == pytest.approx(g["ref_total"][0], rel=1e-12)
+
+
+def test_full_population_golden_is_consistent(th2, th2_uniform):
+    """tests/golden/th2_uniform_full.npz: all 1024 rows of the population bench.py times.
+    Its first 128 rows are the th2_uniform set; the knock-down cost recomputed from the stored
+    ratio vectors (reference's own compiled ode plugin inside the restated a4 loop) equals
+    what the reference's compiled a4 returned; the restatement reproduces a few rows."""
+    g = load_golden("th2_uniform_full")
+    p = th2
+    X = np.random.default_rng(int(g["seed"])).uniform(p["lb"], p["ub"], size=(int(g["rows"]), 87))
+    assert X.sum() == float(g["x_checksum"])
+    np.testing.assert_array_equal(X[:128], th2_uniform["X"])
+    np.testing.assert_array_equal(g["ref_total"][:128], th2_uniform["ref_total"])
+    np.testing.assert_array_equal(g["ref_cost_main"][:128], th2_uniform["ref_cost_main"])
+    np.testing.assert_array_equal(g["ref_pert_cost_from_sim"], g["ref_pert_cost"])
+    assert np.isfinite(g["ref_total"]).all()
+    pflat = p["pert"][:, :12].flatten()
+    for i in (200, 415, 798, 1023):
+        pc, sim, ctrl = orc.perturbation_cost(p["pert"], 12, p["y0"], X[i], p["vector_map"],
+                                              p["mask"], return_controls=True)
+        np.testing.assert_allclose(sim, g["ref_sim"][i], rtol=1e-9)
+        np.testing.assert_allclose(ctrl, g["ref_ctrl_end"][i], rtol=1e-9, atol=1e-300)
+        assert pc == pytest.approx(g["ref_pert_cost"][i], rel=1e-9)
+        assert orc.rank1_residual(g["ref_sim"][i], pflat) == pytest.approx(pc, rel=1e-9)

@@ -27,15 +27,20 @@ def test_noalloc_entry_point_matches_eval_device_twice():
     with torch.cuda.stream(side):
         # two different batches, the second smaller than the first, so stale
         # counters or end states from call one would show up in call two
-        for lo, hi in ((0, 96), (96, 128)):
+        for call, (lo, hi) in enumerate(((0, 96), (96, 128))):
             X = torch.from_numpy(np.ascontiguousarray(g["X"][lo:hi])).cuda()
             N = X.shape[0]
             want = torch.empty(N, dtype=torch.float64, device="cuda")
             got = torch.full((N,), float("nan"), dtype=torch.float64, device="cuda")
             eng.eval_device(N, X.data_ptr(), want.data_ptr(), stream=side.cuda_stream)
             side.synchronize()
+            free_before = torch.cuda.mem_get_info()[0]          # cudaMemGetInfo
             eng.eval_device_noalloc(N, X.data_ptr(), got.data_ptr(), stream=side.cuda_stream)
             side.synchronize()
+            if call == 1:
+                # the promise itself: the device's free memory does not move (checked on the
+                # second call; the first one may still load the library's kernel image lazily)
+                assert torch.cuda.mem_get_info()[0] == free_before
             # same kernel, same inputs: the reduction tolerance of the parity tests
             np.testing.assert_allclose(got.cpu().numpy(), want.cpu().numpy(), rtol=1e-12)
             assert np.isfinite(got.cpu().numpy()).all()
