@@ -1,34 +1,49 @@
 #!/usr/bin/env python
 """
-bench.py - cost-function evaluations per second on BASELINE.json's config 2:
-the Th2 core problem (12 genes, 63 edges, 6 sample times, 12 knock-down rows ->
-15 ODE solves per candidate), one DE population of 1024 candidates per GPU.
+bench.py - cost-function evaluations per second of the LASSIM hot path.
 
   python bench.py --gpus N --steps K --warmup W            this repo's CUDA path
   python bench.py --impl reference --steps K --warmup W    the reference's CPU path
+  python bench.py --config {3,4,5} [--gpus N]              BASELINE.json's other configs
 
-One "step" = one pass of the hot path over one population (1024 candidates =
-15,360 trajectories + the fused cost reductions).  With N > 1 (torchrun) every
-rank evaluates its own copy of that population (islands are independent: weak
-scaling with equal work per GPU, no data-path collective); `value` = candidates
-all ranks evaluated / max-over-ranks device time.
+Headline (BASELINE.json config 2): the Th2 core problem (12 genes, 63 edges, 6 sample
+times, 12 knock-down rows -> 15 ODE solves per candidate), a DE population of 1024
+candidates per GPU.
+
+N = 1   one "step" = one pass of the hot path over the seed-0 population (1024 candidates =
+        15,360 trajectories + the fused cost reductions), device-resident; `e2e` is the
+        same through lassim_eval with host buffers.
+N > 1   the island archipelago of the reference (source/core/base_optimization.py:159-203,
+        ring topology source/lassim_core.py:127), one island of 1024 individuals per GPU,
+        a DIFFERENT random population on every rank: one "step" = one DE generation of every
+        island (trial vectors -> cost evaluation -> selection, on the device), and after
+        every `gen` = 2 steps (examples/optimization_de.json) the best individuals migrate
+        round the ring: one NCCL all-reduce of [islands, dim + 1] doubles INSIDE the timed
+        region.  Ranks do not wait for each other between migrations.  `value` = candidates
+        all ranks evaluated / max-over-ranks device time.  `multi_gpu` carries the evidence
+        that the exchange ran; `replicas` is the round-1 measurement (every rank the same
+        population, no collective) kept as a labelled diagnostic.
 
 Prints ONE JSON line (rank 0).  Keys beyond the base contract:
-  roofline      FP64-FMA roofline of the evaluation kernel (the path is
-                compute-bound: ~0.7 KB of HBM traffic per candidate against
-                ~6e7 flops).  achieved = step attempts counted by
-                the kernels x algorithmic flops per attempt (lassim_flops_per_attempt
-                for the explicit pair, lassim_series_flops_per_attempt for the attempts
-                of the stage-parallel kernel) / device time of the evaluation; peak = DFMA
-                throughput measured in this run by a register-resident probe
-                kernel (MEASURED_PEAKS.json holds no FP64 figure).
-  cpu_baseline  the reference's own compiled Cython functions (oracle/_ref) -
-                or the oracle port when they are absent - on all host cores,
-                on a bounded sample of the same population.
+  roofline      FP64-FMA roofline (the path is compute-bound: ~0.7 KB of HBM traffic per
+                candidate against ~1e7 flops) of the dominant kernel:
+                achieved = step attempts counted by the kernel x algorithmic flops per
+                attempt / its own launch duration (CUDA events on its stream); peak = DFMA
+                throughput measured in this run by a register-resident probe kernel
+                (MEASURED_PEAKS.json holds no FP64 figure).
+  parity        the costs the timed kernels produced against the reference's own outputs
+                for the same 1024 rows (tests/golden/th2_uniform_full.npz) and against the
+                CPU arm's costs computed in this run.
+  cpu_baseline  the reference's own compiled Cython functions (oracle/_ref) - or the
+                oracle port when they are absent - on all host cores, on a bounded sample
+                of the same population.
+  other_configs BASELINE.json configs 3, 4 and 5 on this GPU with their own CPU samples
+                (outside the timed region).
 """
+import os
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")   # before any CUDA call: see Ctx
 import argparse
 import json
-import os
 import subprocess
 import sys
 import threading
@@ -38,19 +53,90 @@ import numpy as np
 
 REPO = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, REPO)
+sys.path.insert(0, os.path.join(REPO, "tools"))
 
 POP = 1024
 PERT_FACTOR = 0.5
+DE_GEN = 2            # generations per evolve round (examples/optimization_de.json)
+DE_VARIANT, DE_F, DE_CR = 3, 0.85, 1.0
 METRIC = "cost-function evals/sec (batched GRN ODE solves)"
 UNIT = "evals/s"
+INTEGRATORS = {"dop853": "Dormand-Prince 8(5,3)", "dp45": "Dormand-Prince 5(4)"}
 
 
 def load_th2():
     return dict(np.load(os.path.join(REPO, "tests", "golden", "th2_problem.npz")))
 
 
-def population(p, seed):
-    return np.random.default_rng(seed).uniform(p["lb"], p["ub"], size=(POP, p["lb"].size))
+def population(p, seed, count=POP):
+    return np.random.default_rng(seed).uniform(p["lb"], p["ub"], size=(count, p["lb"].size))
+
+
+def rel(a, b):
+    with np.errstate(all="ignore"):
+        return np.abs(a - b) / np.abs(b)
+
+
+# --------------------------------------------------------------------------
+# Workloads of the other configs (tools/workloads.py holds the seeded problems)
+# --------------------------------------------------------------------------
+def config_problem(config):
+    from workloads import stiff_population, synthetic_problem, uniform_population
+    if config == 2:
+        p = load_th2()
+        return p, population(p, 0)
+    if config == 3:
+        p = synthetic_problem(50, seed=50)
+        return p, uniform_population(p["lb"], p["ub"], 1024, seed=50)
+    if config == 4:
+        p = synthetic_problem(200, seed=200)
+        return p, stiff_population(p, 8192, seed=200)
+    raise ValueError(config)
+
+
+def peripheral_workload(genes=10000, individuals=16):
+    """Config 5: `genes` peripheral genes against the best Th2 core of the late golden set,
+    `individuals` uniform candidates each (no reference implementation: README.md:77-80)."""
+    th2 = load_th2()
+    g = dict(np.load(os.path.join(REPO, "tests", "golden", "th2_late.npz")))
+    core_x = g["X"][int(np.argmin(g["ref_cost_main"]))]
+    rng = np.random.default_rng(5)
+    data = rng.uniform(0.05, 1.0, (genes, 6))
+    data /= data.max(axis=1, keepdims=True)
+    y0 = rng.uniform(0.05, 1.5, genes)
+    lb = np.concatenate([[0, 0], np.full(12, -20.0)])
+    ub = np.full(14, 20.0)
+    Xp = rng.uniform(lb, ub, size=(genes * individuals, 14))
+    gene = np.repeat(np.arange(genes, dtype=np.int32), individuals)
+    return th2, core_x, data, np.full(genes, 0.2), y0, gene, Xp
+
+
+CONFIG_TEXT = {
+    2: "Th2 core (examples/Th2_lassim_core_TF_network.tsv + data_p1-p4 + knock_data): n=12, "
+       "nnz=63, dim=87, T=6, 15 ODE solves per candidate; DE population 1024 per GPU, uniform "
+       "in default bounds",
+    3: "synthetic 50-gene core (in-degree 5, nnz=250, dim=350, 52 ODE solves per candidate), "
+       "8 islands x 128 individuals, uniform in default bounds, default_rng(50)",
+    4: "synthetic 200-gene core (in-degree 5, nnz=1000, dim=1400, 202 ODE solves per "
+       "candidate), population 8192, stiff regime lambda,vmax~U[10,20], default_rng(200)",
+    5: "peripheral-gene sweep: 10,000 genes x 16 candidates against the fixed Th2 core "
+       "(one joint 13-state solve per candidate; no reference implementation exists)",
+}
+
+
+def workload_config(config, n_gpus):
+    """Identical for both arms of a run (--impl ours / reference)."""
+    if config == 2:
+        par = ("one batch of 1024 on one GPU" if n_gpus == 1 else
+               "island archipelago: one island of 1024 per GPU (distinct random populations), "
+               "DE rand-to-best/1/exp f=0.85 cr=1, ring migration of the best individual every "
+               "%d generations by one all-reduce" % DE_GEN)
+        return {"workload": CONFIG_TEXT[2], "population_per_gpu": POP,
+                "trajectories_per_candidate": 15, "pert_factor": PERT_FACTOR,
+                "rtol": 1.49012e-8, "atol": 1.49012e-8, "parallelism": par}
+    return {"workload": CONFIG_TEXT[config], "pert_factor": PERT_FACTOR,
+            "rtol": 1.49012e-8, "atol": 1.49012e-8,
+            "parallelism": "sharded over %d GPU(s), no data-path collective" % n_gpus}
 
 
 # --------------------------------------------------------------------------
@@ -59,13 +145,16 @@ def population(p, seed):
 _W = {}
 
 
-def _cpu_init(p):
+def _cpu_init(p, extra=None):
     sys.path.insert(0, os.path.join(REPO, "oracle"))
     import lassim_oracle as orc
+    import warnings
+    warnings.simplefilter("ignore")
     np.seterr(all="ignore")
     _W["p"] = p
     _W["orc"] = orc
     _W["ref"] = orc.load_reference_functions()
+    _W["extra"] = extra
 
 
 def _cpu_eval(x):
@@ -73,9 +162,34 @@ def _cpu_eval(x):
     if _W["ref"] is not None:
         return orc.reference_total_cost(x, p["data"], p["sigma"], p["times"], p["y0"],
                                         p["pert"], PERT_FACTOR, p["vector_map"], p["mask"],
-                                        _W["ref"])[0]
+                                        _W["ref"])
     return orc.total_cost(x, p["data"], p["sigma"], p["times"], p["y0"], p["pert"],
-                          PERT_FACTOR, p["vector_map"], p["mask"])[0]
+                          PERT_FACTOR, p["vector_map"], p["mask"])
+
+
+def _cpu_partial(x):
+    """Config 4 (202 solves of ~1 s each per candidate): the time series, the control and the
+    first `extra` knocked rows of one candidate; returns the number of solves done."""
+    p, orc = _W["p"], _W["orc"]
+    n = p["y0"].size
+    ode = _W["ref"][0] if _W["ref"] is not None else orc.odeint_lassim
+    sol = np.array(x, dtype=np.float64)
+    vm = lambda: np.array(p["vector_map"], dtype=np.float64).copy()
+    ode(p["y0"], p["times"], sol.copy(), vm(), p["mask"], n, np.empty(n))
+    tt = p["pert"][0, n:]
+    ode(p["y0"], tt, sol.copy(), vm(), p["mask"], n, np.empty(n))
+    rows = int(_W["extra"])
+    for i in range(rows):
+        sol[i] *= p["pert"][i, i]
+        ode(p["y0"], tt, sol.copy(), vm(), p["mask"], n, np.empty(n))
+    return 2 + rows
+
+
+def _cpu_peripheral(args):
+    gene, xp = args
+    th2, core_x, data, sigma, y0 = _W["extra"]
+    return _W["orc"].peripheral_cost(xp, core_x, th2["times"], th2["y0"], th2["vector_map"],
+                                     th2["mask"], data[gene], sigma[gene], y0[gene])
 
 
 def cpu_kind():
@@ -87,54 +201,58 @@ def cpu_kind():
 class CpuArm:
     """All-host-cores pool running the reference path on samples of X."""
 
-    def __init__(self, p):
+    def __init__(self, p, extra=None):
         from multiprocessing import get_context
         self.cores = os.cpu_count() or 1
-        self.pool = get_context("fork").Pool(self.cores, initializer=_cpu_init, initargs=(p,))
+        self.pool = get_context("fork").Pool(self.cores, initializer=_cpu_init,
+                                             initargs=(p, extra))
         self.kind = cpu_kind()
 
-    def run(self, X):
+    def run(self, X, fn=_cpu_eval):
         t0 = time.perf_counter()
-        costs = self.pool.map(_cpu_eval, list(X), chunksize=1)
-        return time.perf_counter() - t0, np.array(costs)
+        out = self.pool.map(fn, list(X), chunksize=1)
+        return time.perf_counter() - t0, out
 
     def close(self):
         self.pool.close()
         self.pool.join()
 
 
-def sample_size(cores, per_core):
-    return int(min(POP, max(8, per_core * cores)))
+def path_text(kind):
+    return ("reference's compiled Cython functions (oracle/_ref)" if kind == "reference"
+            else "oracle port (scipy.integrate.odeint)") + " + LSODA, one worker per core"
 
 
 def run_reference_arm(args):
+    """The reference's CPU path on the headline workload.  Steps are bounded samples of the
+    population (8 candidates per core each, consecutive rows, wrapping); the K samples go
+    through the pool as ONE stream of work, so a slow candidate at the end of a sample does
+    not leave the other cores idle (the GPU arm's steps do end with a synchronisation): the
+    arm is timed the way that suits the CPU best."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    if args.config != 2:
+        return run_reference_other(args)
     p = load_th2()
     X = population(p, 0)
     arm = CpuArm(p)
-    S = sample_size(arm.cores, 4)
-    for w in range(args.warmup):
+    S = int(min(POP, max(64, 8 * arm.cores)))
+    for w in range(max(args.warmup, 1)):
         arm.run(X[:max(arm.cores, 8)])
-    total = 0.0
-    for k in range(args.steps):
-        lo = (k * S) % POP
-        idx = (lo + np.arange(S)) % POP
-        dt, _ = arm.run(X[idx])
-        total += dt
+    idx = np.arange(S * args.steps) % POP
+    total, _ = arm.run(X[idx])
     arm.close()
     value = S * args.steps / total
-    sample = ("%d candidates per step (consecutive rows of the seed-0 population of %d), "
-              "%s LSODA path, one worker per core" % (S, POP,
-              "reference's compiled Cython functions (oracle/_ref)" if arm.kind == "reference"
-              else "oracle port (scipy.integrate.odeint)"))
+    sample = ("%d candidates per step (consecutive rows of the seed-0 population of %d, "
+              "wrapping), %d steps pooled as one stream of work; %s"
+              % (S, POP, args.steps, path_text(arm.kind)))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(1, "cpu"),
+        "config": workload_config(2, args.gpus),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": arm.cores,
                          "kind": arm.kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0,
@@ -143,17 +261,56 @@ def run_reference_arm(args):
     print(json.dumps(line), flush=True)
 
 
+def cpu_sample_other(config):
+    """Bounded CPU sample for configs 3, 4, 5 -> cpu_baseline dict."""
+    if config == 3:
+        p, X = config_problem(3)
+        arm = CpuArm(p)
+        S = 2 * arm.cores
+        dt, _ = arm.run(X[:S])
+        arm.close()
+        return {"value": S / dt, "unit": UNIT, "cores": arm.cores, "kind": arm.kind,
+                "sample": "first %d candidates of the population (2 per core), one pass "
+                          "(%.1f s); %s" % (S, dt, path_text(arm.kind))}
+    if config == 4:
+        p, X = config_problem(4)
+        rows = 2
+        arm = CpuArm(p, extra=rows)
+        S = arm.cores
+        dt, solves = arm.run(X[:S], _cpu_partial)
+        arm.close()
+        K = 2 + p["y0"].size
+        per_solve = dt * arm.cores / float(sum(solves))
+        return {"value": arm.cores / (per_solve * K), "unit": UNIT, "cores": arm.cores,
+                "kind": arm.kind,
+                "sample": "one candidate per core, %d of its %d ODE solves (time series, control, "
+                          "first %d knocked rows: %.1f s), extrapolated linearly in the number of "
+                          "solves - a whole evaluation is ~%.0f s per core; %s"
+                          % (2 + rows, K, rows, dt, per_solve * K, path_text(arm.kind))}
+    th2, core_x, data, sigma, y0, gene, Xp = peripheral_workload()
+    arm = CpuArm(th2, extra=(th2, core_x, data, sigma, y0))
+    S = 64 * arm.cores
+    dt, _ = arm.run(list(zip(gene[:S], Xp[:S])), _cpu_peripheral)
+    arm.close()
+    return {"value": S / dt, "unit": UNIT, "cores": arm.cores, "kind": "port",
+            "sample": "first %d candidates (64 per core), one pass (%.1f s); oracle's "
+                      "peripheral_cost (joint 13-state system through LSODA), parity unpinned: "
+                      "the reference has no peripheral-gene code" % (S, dt)}
+
+
+def run_reference_other(args):
+    cb = cpu_sample_other(args.config)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT,
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": None, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args.config, args.gpus), "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
 # --------------------------------------------------------------------------
-def workload_config(n_gpus, l2_note):
-    return {"workload": "Th2 core (examples/Th2_lassim_core_TF_network.tsv + data_p1-p4 + "
-                        "knock_data): n=12, nnz=63, dim=87, T=6, 15 ODE solves per candidate; "
-                        "DE population 1024 per GPU, uniform in default bounds, default_rng(0) on every rank",
-            "population_per_gpu": POP, "trajectories_per_candidate": 15,
-            "pert_factor": PERT_FACTOR, "rtol": 1.49012e-8, "atol": 1.49012e-8,
-            "parallelism": "islands x%d (independent populations, no collective)" % n_gpus,
-            "l2": l2_note}
-
-
 class ClockSampler(threading.Thread):
     """nvidia-smi clocks line sampled while the timed region runs."""
 
@@ -198,71 +355,286 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def run_ours(args):
-    import torch
-    import torch.distributed as dist
+class Ctx:
+    """torch / distributed plumbing shared by the GPU legs."""
+
+    def __init__(self):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback "
+                             "(use --impl reference for the CPU reference arm)")
+        # before the CUDA context exists: the islands' streams need hardware queues of their own
+        os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+        torch.cuda.set_device(self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+        # a side stream: the legacy default stream's handle is 0, which the C ABI reads as
+        # "the engine's own stream"; events must be on the launch stream
+        self.side = torch.cuda.Stream()
+        torch.cuda.set_stream(self.side)
+        self.stream = self.side.cuda_stream
+        assert self.stream != 0
+        self.flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, values):
+        t = self.torch.tensor(values, dtype=self.torch.float64, device="cuda")
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return [float(v) for v in t]
+
+    def sum_over_ranks(self, values):
+        t = self.torch.tensor(values, dtype=self.torch.float64, device="cuda")
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return [float(v) for v in t]
+
+    def close(self):
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
+def th2_engine(ctx, method):
     from lassim_b200 import Engine
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback "
-                         "(use --impl reference for the CPU reference arm)")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-
     p = load_th2()
-    X = population(p, 0)      # the config-2 population on every rank: equal work per GPU
-    eng = Engine(local)
-    eng.set_method(args.method)
+    eng = Engine(ctx.local)
+    eng.set_method(method)
     eng.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"], p["pert"], PERT_FACTOR)
-    flops_per_attempt = eng.flops_per_attempt      # SURVEY.md 8d, per integrator
-    # long time series leave the standard kernel after a cap of attempts and continue in the
-    # stage-parallel Gauss kernel (two warps per trajectory), with its own attempts and flops
-    series_flops = eng.series_flops_per_attempt(POP)
+    return p, eng
 
+
+# --------------------------------------------------------------------------
+# parity of the timed results
+# --------------------------------------------------------------------------
+def mixed_err(a, ref, scale):
+    with np.errstate(all="ignore"):
+        e = np.abs(a - ref) / np.maximum(np.abs(ref), scale)
+    return np.where(np.isfinite(a) & np.isfinite(ref), e, np.where(a == ref, 0.0, np.inf))
+
+
+def parity_block(out, cpu=None):
+    """`out`: details of the GPU evaluation of the seed-0 population (host arrays).
+    Against tests/golden/th2_uniform_full.npz = the reference's own outputs for the same
+    1024 rows, gated where the reference is converged (agrees with rtol = atol = 1e-13 to
+    1e-7); and against the CPU arm's costs of this run (`cpu` = (rows, costs))."""
+    g = dict(np.load(os.path.join(REPO, "tests", "golden", "th2_uniform_full.npz")))
+    ref_m, tight_m = g["ref_cost_main"], g["tight_cost_main"]
+    ref_p, tight_p = g["ref_pert_cost"], g["tight_pert_cost"]
+    main_ok = rel(ref_m, tight_m) <= 1e-7
+    pert_ok = rel(ref_p, tight_p) <= 1e-7
+    both = main_ok & pert_ok
+    e_m, e_p, e_t = rel(out["cost_main"], ref_m), rel(out["pert_cost"], ref_p), \
+        rel(out["cost"], g["ref_total"])
+    nan_gpu = ~np.isfinite(out["cost"])
+    nan_ref = ~np.isfinite(g["ref_total"])
+    block = {
+        "rows": int(len(ref_m)),
+        "source": "tests/golden/th2_uniform_full.npz (reference's own _objfun_impl and compiled "
+                  "Cython functions on the same seed-0 rows, oracle/gen_golden.py)",
+        "converged_rows": {"cost_main": int(main_ok.sum()), "pert_cost": int(pert_ok.sum()),
+                           "total": int(both.sum())},
+        "max_rel_cost_main_converged": float(e_m[main_ok].max()),
+        "max_rel_cost_main_vs_tight_all": float(rel(out["cost_main"], tight_m).max()),
+        "max_rel_pert_cost_converged": float(np.nanmax(e_p[pert_ok])),
+        "max_rel_total_converged": float(np.nanmax(e_t[both])),
+        "frac_total_within_1e-6": float(np.mean(e_t <= 1e-6)),
+        "frac_total_within_1e-6_reference_vs_its_converged_answer": float(np.mean(
+            rel(g["ref_total"], PERT_FACTOR * tight_p + tight_m) <= 1e-6)),
+        "nan_rows_gpu": [int(i) for i in np.flatnonzero(nan_gpu)],
+        "nan_rows_ref": [int(i) for i in np.flatnonzero(nan_ref)],
+        "nan_rows_agree": bool(np.array_equal(nan_gpu, nan_ref)),
+        "status_not_ok": int((out["status"] != 0).sum()),
+    }
+    loose = ~main_ok
+    loose_ok = bool((rel(out["cost_main"], tight_m)[loose]
+                     <= np.maximum(1e-5, 25 * rel(ref_m, tight_m)[loose])).all())
+    block["cost_main_unconverged_rows_within_25x_reference_error"] = loose_ok
+    ok = (block["max_rel_cost_main_converged"] <= 1e-6 and loose_ok and block["status_not_ok"] == 0
+          and int(nan_gpu.sum()) <= len(ref_m) // 200)
+    block["knock_down_cost_note"] = (
+        "reported, not gated: every uniform candidate has control end states that decayed to "
+        "1e-30..1e-170, which the cost divides by; LSODA's BDF keeps such remnants accurate in the "
+        "relative sense (median 5e-4 down to 1e-50), an explicit pair keeps them to atol only, so "
+        "the costs agree where no remnant matters (fractions above) - see tests/test_gpu_parity.py"
+        "::test_full_population_against_the_reference")
+    if "E" in out:
+        # end states of the 14 knock-down solves against the converged ones / the reference's own
+        ref_ends = np.concatenate([g["ref_ctrl_end"], g["ref_knock_end"]], axis=1)
+        tight_ends = np.concatenate([g["tight_ctrl_end"], g["tight_knock_end"]], axis=1)
+        scale = load_th2()["y0"][None, None, :]
+        ref_off = mixed_err(ref_ends, tight_ends, scale).max(axis=(1, 2))
+        e_tight = mixed_err(out["E"][:, 1:], tight_ends, scale).max(axis=(1, 2))
+        e_ref = mixed_err(out["E"][:, 1:], ref_ends, scale).max(axis=(1, 2))
+        conv = ref_off <= 1e-5
+        block["knock_down_end_states"] = {
+            "tolerance": "|a - b| / max(|b|, y0) <= 1e-5 over the 14 x 12 end states of a row",
+            "rows_within_1e-5_of_converged": int((e_tight <= 1e-5).sum()),
+            "rows_within_1e-5_of_converged_reference": int(conv.sum()),
+            "rows_within_1e-5_plus_reference_error_of_reference": int((e_ref <= 1e-5 + ref_off).sum()),
+            "max_vs_converged_where_reference_converged": float(e_tight[conv].max()),
+            "max_reference_vs_converged": float(ref_off.max())}
+        ok = ok and (e_tight <= 1e-5).mean() >= 0.99 and float(e_tight[conv].max()) <= 5e-5
+    if cpu is not None:
+        rows, costs = cpu
+        costs = np.asarray(costs)              # (total, cost_main, pert_cost) per row
+        same = np.allclose(costs[:, 0], g["ref_total"][rows], rtol=1e-9, equal_nan=True)
+        block["cpu_arm_of_this_run"] = {
+            "rows": int(len(rows)), "reproduces_golden": bool(same),
+            "max_rel_cost_main_converged": float(rel(out["cost_main"][rows], costs[:, 1])[main_ok[rows]].max()),
+            "max_rel_total_converged": float(np.nanmax(rel(out["cost"][rows], costs[:, 0])[both[rows]])),
+        }
+        ok = ok and block["cpu_arm_of_this_run"]["max_rel_cost_main_converged"] <= 1e-6 \
+            and block["cpu_arm_of_this_run"]["max_rel_total_converged"] <= 1e-6
+    block["ok"] = bool(ok)
+    return block
+
+
+# --------------------------------------------------------------------------
+# GPU legs
+# --------------------------------------------------------------------------
+def roofline_of_one_evaluation(ctx, eng, dX, peak, reps=3):
+    """Dominant kernel of one evaluation of dX (device tensor [POP, dim]) on the main
+    scratch: its own launch time, attempts and algorithmic flops."""
+    torch = ctx.torch
+    N = dX.shape[0]
+    dcost = torch.empty(N, dtype=torch.float64, device="cuda")
+    dcnt = torch.zeros(N * 3, dtype=torch.int64, device="cuda")
+    k_ms, sp_ms, sp_att, att = [], [], [], []
+    for _ in range(reps):
+        ctx.flush.zero_()
+        eng.eval_device(N, dX.data_ptr(), dcost.data_ptr(), None, None, None, dcnt.data_ptr(),
+                        ctx.stream)
+        torch.cuda.synchronize()
+        k_ms.append(eng.last_kernel_ms())
+        sp_ms.append(eng.last_stage_parallel_ms())
+        sp_att.append(eng.last_stage_parallel_attempts())
+        att.append(int(dcnt.view(N, 3)[:, :2].sum().item()))
+    return roofline_dict(eng, N, peak, np.mean(k_ms), np.mean(sp_ms), np.mean(sp_att), np.mean(att))
+
+
+def roofline_dict(eng, N, peak, k_ms, d_ms, series_attempts, attempts):
+    flops_per_attempt = eng.flops_per_attempt
+    series_flops = eng.series_flops_per_attempt(N)
+    flops = (attempts - series_attempts) * flops_per_attempt + series_attempts * series_flops
+    achieved_all = flops / (k_ms * 1e-3) / 1e12
+    achieved = series_attempts * series_flops / (d_ms * 1e-3) / 1e12
+    return {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+            "frac": achieved / peak if peak else None,
+            "traffic": None,
+            "traffic_note": "the path is compute-bound (X in + cost out = 0.72 MB per step); the "
+                            "dram bytes of the three kernels are in profiles/ (ncu --set full), "
+                            "not re-measured in this run",
+            "kernel": eng.series_kernel_name(N), "kernel_ms": d_ms,
+            "attempts_per_launch": series_attempts, "flops_per_attempt": series_flops,
+            "share_of_step": d_ms / k_ms,
+            "note": "dominant kernel of the step: 2-3 limit-cycle time series of ~12,000 "
+                    "sequential attempts each set its duration (latency-bound)",
+            "evaluation": {"kernels": [eng.kernel_name + " (time series until handed over)",
+                                       eng.series_kernel_name(N),
+                                       eng.kernel_name + " (knock-downs, second stream)"],
+                           "ms": k_ms, "achieved": achieved_all,
+                           "frac": achieved_all / peak if peak else None,
+                           "step_attempts": attempts,
+                           "explicit_pair_flops_per_attempt": flops_per_attempt},
+            "peak_source": "in-run DFMA probe kernel (MEASURED_PEAKS.json has HBM and bf16 "
+                           "figures only)"}
+
+
+def machine_full(ctx, eng, dX, peak, reps=16):
+    torch = ctx.torch
+    dXs = dX.repeat(reps, 1).contiguous()
+    N = dXs.shape[0]
+    dcs = torch.empty(N, dtype=torch.float64, device="cuda")
+    dns = torch.zeros(N * 3, dtype=torch.int64, device="cuda")
+    for _ in range(2):
+        eng.eval_device(N, dXs.data_ptr(), dcs.data_ptr(), None, None, None, dns.data_ptr(),
+                        ctx.stream)
+    torch.cuda.synchronize()
+    ms = eng.last_kernel_ms()
+    att = int(dns.view(-1, 3)[:, :2].sum().item())
+    att_series = eng.last_stage_parallel_attempts()
+    flops = (att - att_series) * eng.flops_per_attempt + att_series * eng.series_flops_per_attempt(N)
+    tf = flops / (ms * 1e-3) / 1e12
+    return {"candidates": N, "kernel_ms": ms, "evals_per_s": N / (ms * 1e-3),
+            "time_series_kernel": eng.series_kernel_name(N), "achieved_tflops": tf,
+            "frac": tf / peak if peak else None,
+            "note": "same kernels on 16 copies of the population in one call (outside the timed "
+                    "region): what they do when the batch outlasts its longest trajectory"}
+
+
+def async_islands(ctx, eng, p, islands=8, individuals=128, generations=20, seed=77):
+    """One GPU, `islands` islands evolving concurrently (lanes) against the same islands in
+    lockstep (one batch per generation): fills the time a single batch spends waiting for its
+    slowest candidate."""
+    torch = ctx.torch
+    X0 = np.random.default_rng(seed + ctx.rank).uniform(p["lb"], p["ub"],
+                                                       size=(islands, individuals, p["lb"].size))
+    ext = torch.cuda.ExternalStream(eng.stream)
+    out = {}
+    finals = []
+    for name, lanes in (("lockstep", 1), ("concurrent", 0)):
+        eng.de_init(X0, p["lb"], p["ub"], variant=DE_VARIANT, f=DE_F, cr=DE_CR, seed=seed)
+        eng.de_set_lanes(lanes)
+        eng.de_evolve(1)                       # evaluates the start population + one generation
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(ext)
+        eng.de_evolve(generations)
+        e1.record(ext)
+        e1.synchronize()
+        ms = e0.elapsed_time(e1)
+        out[name] = {"ms": ms, "evals_per_s": islands * individuals * generations / (ms * 1e-3)}
+        finals.append(eng.de_get()[1])
+    eng.de_set_lanes(0)
+    out.update(islands=islands, individuals=individuals, generations=generations,
+               same_result=bool(np.array_equal(finals[0], finals[1])),
+               speedup=out["lockstep"]["ms"] / out["concurrent"]["ms"])
+    return out
+
+
+def run_single(args, ctx):
+    """N = 1: the headline."""
+    torch = ctx.torch
+    p, eng = th2_engine(ctx, args.method)
+    X = population(p, 0)
     dX = torch.from_numpy(X).cuda()
     dcost = torch.empty(POP, dtype=torch.float64, device="cuda")
+    dmain = torch.empty(POP, dtype=torch.float64, device="cuda")
+    dpert = torch.empty(POP, dtype=torch.float64, device="cuda")
     dcnt = torch.zeros(POP * 3, dtype=torch.int64, device="cuda")
     dstatus = torch.zeros(POP, dtype=torch.int32, device="cuda")
-    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
-    # a side stream: the legacy default stream's handle is 0, which the C ABI
-    # reads as "the engine's own stream"; events must be on the launch stream
-    side = torch.cuda.Stream()
-    torch.cuda.set_stream(side)
-    stream = side.cuda_stream
-    assert stream != 0
 
     def step_device():
-        eng.eval_device(POP, dX.data_ptr(), dcost.data_ptr(), None, None,
-                        dstatus.data_ptr(), dcnt.data_ptr(), stream)
+        eng.eval_device(POP, dX.data_ptr(), dcost.data_ptr(), dmain.data_ptr(), dpert.data_ptr(),
+                        dstatus.data_ptr(), dcnt.data_ptr(), ctx.stream)
 
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    fp64_peak = eng.fp64_peak_tflops(400000) if rank == 0 else None
-
-    for _ in range(max(args.warmup, 3)):
-        flush.zero_()
+    fp64_peak = eng.fp64_peak_tflops(400000)
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
+        ctx.flush.zero_()
         step_device()
     torch.cuda.synchronize()
 
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-        time.sleep(0.3)
+    sampler = ClockSampler(ctx.local)
+    sampler.start()
+    time.sleep(0.3)
     launches0 = eng.launch_count
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     kernel_ms, attempts, sp_ms, sp_att = [], [], [], []
-    barrier()
+    ctx.barrier()
     for k in range(args.steps):
-        flush.zero_()                      # evict L2 between timed steps
+        ctx.flush.zero_()                      # evict L2 between timed steps
         starts[k].record()
         step_device()
         ends[k].record()
@@ -271,144 +643,355 @@ def run_ours(args):
         attempts.append(int(dcnt.view(POP, 3)[:, :2].sum().item()))
         sp_ms.append(eng.last_stage_parallel_ms())            # the dominant kernel's own launch
         sp_att.append(eng.last_stage_parallel_attempts())
-    barrier()
+    ctx.barrier()
     launches = eng.launch_count - launches0
     dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
-    # A knock-down cost is NaN in the reference too when a control end state's rounding-level
-    # remnant (1e-190) is negative under a knocked state of 1e120 (-inf/inf after the clip,
-    # perturbation_functions.pyx:86-95): every integration must succeed, all but such rows be finite
-    nonfinite = int((~torch.isfinite(dcost)).sum().item())
-    ok = bool((dstatus == 0).all().item()) and nonfinite <= POP // 200
-
-    # the other Dormand-Prince pair on the same population (outside the timed region):
-    # the headline uses --method (default 8(5,3)); BASELINE.json's north_star names 5(4)
-    other = None
-    if rank == 0 and world == 1:
-        alt = "dp45" if args.method == "dop853" else "dop853"
-        eng.set_method(alt)
-        ms_alt = []
-        for _ in range(3):
-            step_device()
-            torch.cuda.synchronize()
-            ms_alt.append(eng.last_kernel_ms())
-        other = {"integrator": {"dop853": "Dormand-Prince 8(5,3)", "dp45": "Dormand-Prince 5(4)"}[alt],
-                 "kernel_ms": float(np.median(ms_alt[1:])),
-                 "evals_per_s": POP / (float(np.median(ms_alt[1:])) * 1e-3)}
-        eng.set_method(args.method)
-
-    # the same kernel with the machine kept full (16 copies of the population):
-    # separates kernel quality from the single-population critical path
-    sat = None
-    if rank == 0:
-        reps = 16
-        dXs = dX.repeat(reps, 1).contiguous()
-        dcs = torch.empty(POP * reps, dtype=torch.float64, device="cuda")
-        dns = torch.zeros(POP * reps * 3, dtype=torch.int64, device="cuda")
-        for _ in range(2):
-            eng.eval_device(POP * reps, dXs.data_ptr(), dcs.data_ptr(), None, None, None,
-                            dns.data_ptr(), stream)
-        torch.cuda.synchronize()
-        ms_sat = eng.last_kernel_ms()
-        att = int(dns.view(-1, 3)[:, :2].sum().item())
-        att_series = eng.last_stage_parallel_attempts()
-        sat_flops = (att - att_series) * flops_per_attempt + \
-            att_series * eng.series_flops_per_attempt(POP * reps)
-        sat = {"candidates": POP * reps, "kernel_ms": ms_sat,
-               "evals_per_s": POP * reps / (ms_sat * 1e-3),
-               "time_series_kernel": eng.series_kernel_name(POP * reps),
-               "achieved_tflops": sat_flops / (ms_sat * 1e-3) / 1e12}
-        del dXs, dcs, dns
+    gpu_out = {"cost": dcost.cpu().numpy(), "cost_main": dmain.cpu().numpy(),
+               "pert_cost": dpert.cpu().numpy(), "status": dstatus.cpu().numpy(),
+               "E": eng.last_end_states(POP)}
 
     # end to end through the public host API (C-ABI lassim_eval, host buffers)
     Xpin = torch.from_numpy(X).pin_memory()
     Xh = Xpin.numpy()
     for _ in range(2):
         eng.eval(Xh)
-    barrier()
+    ctx.barrier()
     t0 = time.perf_counter()
     for k in range(args.steps):
         cost_h = eng.eval(Xh)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
-    barrier()
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop()
+    e2e_same = bool(np.array_equal(cost_h, gpu_out["cost"], equal_nan=True))
 
-    t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms_max, e2e_ms_max = float(t[0]), float(t[1])
+    value = POP * args.steps / (dev_ms * 1e-3)
+    roof = roofline_dict(eng, POP, fp64_peak, float(np.mean(kernel_ms)), float(np.mean(sp_ms)),
+                         float(np.mean(sp_att)), float(np.mean(attempts)))
+    # the integrator-independent figure of SURVEY.md 8d: right-hand sides LSODA itself needs
+    # for these 1024 evaluations x algorithmic flops of one, over the device time of a step
+    g = dict(np.load(os.path.join(REPO, "tests", "golden", "th2_uniform_full.npz")))
+    if "lsoda_nfe_total" in g:
+        f_rhs = 2 * 63 + 5 * 12
+        useful = float(g["lsoda_nfe_total"].sum()) * f_rhs / (dev_ms / args.steps * 1e-3) / 1e12
+        roof["lsoda_equivalent"] = {
+            "achieved": useful, "frac": useful / fp64_peak,
+            "note": "sum over the 1024 candidates of LSODA's own nfe (all 15 solves, reference "
+                    "tolerances; tests/golden/th2_uniform_full.npz) x F_rhs = 2 nnz + 5 n = %d "
+                    "flops / device time of a step" % f_rhs}
+    roof["machine_full"] = machine_full(ctx, eng, dX, fp64_peak)
+
+    # the other Dormand-Prince pair on the same population (outside the timed region):
+    # the headline uses --method (default 8(5,3)); BASELINE.json's north_star names 5(4)
+    alt = "dp45" if args.method == "dop853" else "dop853"
+    eng.set_method(alt)
+    ms_alt = []
+    for _ in range(3):
+        step_device()
+        torch.cuda.synchronize()
+        ms_alt.append(eng.last_kernel_ms())
+    other = {"integrator": INTEGRATORS[alt], "kernel_ms": float(np.median(ms_alt[1:])),
+             "evals_per_s": POP / (float(np.median(ms_alt[1:])) * 1e-3)}
+    eng.set_method(args.method)
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1,
+        "steps": args.steps, "warmup": warm,
+        "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(2, 1),
+        "notes": {"integrator": INTEGRATORS[args.method],
+                  "l2": "flushed between timed steps (256 MiB write); per-step CUDA events on "
+                        "the launching stream",
+                  "population": "default_rng(0).uniform(lb, ub, (1024, 87))"},
+        "e2e": {"value": POP * args.steps / e2e_s, "unit": UNIT,
+                "h2d_bytes_per_step": int(X.nbytes), "d2h_bytes_per_step": int(POP * 8),
+                "api": "lassim_eval (C ABI) with pinned host X, host cost out",
+                "same_costs_as_device_path": e2e_same},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": roof,
+        "other_integrator": other,
+    }
+    cpu = None
+    if not args.no_cpu_baseline:
+        arm = CpuArm(p)
+        S = int(min(POP, max(8, 32 * arm.cores)))   # ~10-20 s: includes the slow candidates
+        dt, costs = arm.run(X[:S])
+        arm.close()
+        cpu = (np.arange(S), costs)
+        line["cpu_baseline"] = {
+            "value": S / dt, "unit": UNIT, "cores": arm.cores, "kind": arm.kind,
+            "sample": "first %d candidates of the same population, one pass (%.1f s); %s"
+                      % (S, dt, path_text(arm.kind))}
+    line["parity"] = parity_block(gpu_out, cpu)
+    line["results_ok"] = bool(line["parity"]["ok"] and e2e_same)
+    line["nonfinite_costs"] = len(line["parity"]["nan_rows_gpu"])
+    line["async_islands"] = async_islands(ctx, eng, p)
+    if not args.no_other_configs:
+        line["other_configs"] = {}
+        for c in (3, 4, 5):
+            try:
+                line["other_configs"]["config%d" % c] = other_config(
+                    args, ctx, c, fp64_peak, with_cpu=not args.no_cpu_baseline)
+            except Exception as exc:                      # a diagnostic must not lose the headline
+                line["other_configs"]["config%d" % c] = {"error": repr(exc)}
+    print(json.dumps(line), flush=True)
+
+
+def migrate(ctx, eng, n_islands):
+    """PyGMO's default migration on a ring: every island sends its best, which replaces the
+    receiver's worst if better (one all-reduce of the table of bests; rows are disjoint)."""
+    torch = ctx.torch
+    t0 = time.perf_counter()
+    mine = eng.de_best()                                      # synchronises the engine
+    table = np.zeros((n_islands, mine.shape[1]))
+    table[ctx.rank::ctx.world] = mine
+    t = torch.from_numpy(table).cuda()
+    if ctx.world > 1:
+        ctx.dist.all_reduce(t)
+    table = t.cpu().numpy()
+    eng.de_migrate_ring(table, ctx.rank, ctx.world)
+    return table, (time.perf_counter() - t0) * 1e3
+
+
+def run_archipelago(args, ctx):
+    """N > 1: one island of 1024 per GPU, distinct populations, DE on the device, ring
+    migration by NCCL inside the timed region (see the module docstring)."""
+    torch = ctx.torch
+    p, eng = th2_engine(ctx, args.method)
+    world, rank = ctx.world, ctx.rank
+    dim = p["lb"].size
+    X0 = population(p, 1000 + rank)[None]                    # a different population per rank
+    eng.de_init(X0, p["lb"], p["ub"], variant=DE_VARIANT, f=DE_F, cr=DE_CR, seed=42)
+    eng.de_set_island_ids(rank, world)
+    ext = torch.cuda.ExternalStream(eng.stream)
+    fp64_peak = eng.fp64_peak_tflops(400000) if rank == 0 else None
+
+    warm = max(args.warmup, 3)
+    for k in range(warm):
+        eng.de_evolve(1)
+        if (k + 1) % DE_GEN == 0:
+            migrate(ctx, eng, world)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(ctx.local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    launches0, evals0 = eng.launch_count, eng.de_evaluations
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    mig_ms, migrations = [], 0
+    table = None
+    ctx.barrier()
+    e0.record(ext)
+    for k in range(args.steps):
+        eng.de_evolve(1)                                     # enqueued; no host wait
+        if (k + 1) % DE_GEN == 0:
+            table, ms = migrate(ctx, eng, world)
+            mig_ms.append(ms)
+            migrations += 1
+    e1.record(ext)
+    e1.synchronize()
+    ctx.barrier()
+    dev_ms = e0.elapsed_time(e1)
+    launches = eng.launch_count - launches0
+    evals = eng.de_evaluations - evals0
+    assert evals == POP * args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    dev_ms_max, mig_max = ctx.max_over_ranks([dev_ms, float(np.mean(mig_ms)) if mig_ms else 0.0])
+    dev_ms_min = -ctx.max_over_ranks([-dev_ms])[0]
+    # every rank holds the same table of bests after the all-reduce
+    if table is None:
+        table, _ = migrate(ctx, eng, world)
+    chk = float(np.nansum(table))
+    agree = ctx.max_over_ranks([chk])[0] == -ctx.max_over_ranks([-chk])[0]
+    Xf, Ff = eng.de_get()
+    best = ctx.max_over_ranks([-float(np.nanmin(Ff))])[0] * -1
+
+    # end to end through the public host API: the host-driven archipelago (trial vectors built
+    # on the host, lassim_eval with host buffers every generation, the same migration)
+    from lassim_b200.core.core_problem import CoreProblemFactory
+    from lassim_b200.core.functions.common_functions import odeint1e8_lassim
+    from lassim_b200.core.functions.perturbation_functions import perturbation_func_sequential
+    from lassim_b200.pygmo import algorithm, archipelago, topology
+    prob = CoreProblemFactory.new_instance(
+        (p["data"], p["sigma"], p["times"], p["pert"]), p["y0"], odeint1e8_lassim,
+        perturbation_func_sequential, PERT_FACTOR).build(
+        dim, (list(p["lb"]), list(p["ub"])), (p["vector_map"], p["mask"]))
+    from lassim_b200.core import _engine as engmod
+    engmod.get_engine(ctx.local).set_method(args.method)
+    algo = algorithm.de(gen=DE_GEN, variant=DE_VARIANT, f=DE_F, cr=DE_CR, xtol=0.0, ftol=0.0)
+    archi = archipelago(algo, prob, world, POP, topology=topology.ring(), seed=1000)
+    archi.evolve(1)                                          # start populations + one round
+    ctx.barrier()
+    ev0 = archi.evaluations
+    t0 = time.perf_counter()
+    archi.evolve(args.steps // DE_GEN)
+    if args.steps % DE_GEN:
+        algo.gen = args.steps % DE_GEN
+        archi.evolve(1)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    e2e_evals = archi.evaluations - ev0
+    e2e_ms_max = ctx.max_over_ranks([e2e_s * 1e3])[0]
+    e2e_total = ctx.sum_over_ranks([float(e2e_evals)])[0]
+
+    # round-1 style diagnostic: every rank the same population, no collective
+    dX = torch.from_numpy(population(p, 0)).cuda()
+    dcost = torch.empty(POP, dtype=torch.float64, device="cuda")
+    rs, re = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(2):
+        eng.eval_device(POP, dX.data_ptr(), dcost.data_ptr(), stream=ctx.stream)
+    ctx.barrier()
+    rs.record()
+    for _ in range(5):
+        eng.eval_device(POP, dX.data_ptr(), dcost.data_ptr(), stream=ctx.stream)
+    re.record()
+    re.synchronize()
+    ctx.barrier()
+    rep_ms = ctx.max_over_ranks([rs.elapsed_time(re)])[0]
+    roof = roofline_of_one_evaluation(ctx, eng, torch.from_numpy(Xf[0]).cuda(), fp64_peak) \
+        if rank == 0 else None
+    asy = async_islands(ctx, eng, p)
+    asy_ms = ctx.max_over_ranks([asy["concurrent"]["ms"]])[0]
 
     if rank == 0:
-        value = world * POP * args.steps / (dev_ms_max * 1e-3)
-        e2e_value = world * POP * args.steps / (e2e_ms_max * 1e-3)
-        k_ms = float(np.mean(kernel_ms))
-        series_attempts = float(np.mean(sp_att))
-        flops = (float(np.mean(attempts)) - series_attempts) * flops_per_attempt + \
-            series_attempts * series_flops
-        achieved_all = flops / (k_ms * 1e-3) / 1e12
-        # the dominant kernel: the stage-parallel kernel the long time series are handed to
-        d_ms = float(np.mean(sp_ms))
-        achieved = series_attempts * series_flops / (d_ms * 1e-3) / 1e12
+        roof["note"] = ("one evaluation of rank 0's final population on its own (outside the "
+                        "timed region): " + roof["note"])
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
-            "steps": args.steps, "warmup": max(args.warmup, 3),
+            "metric": METRIC, "value": world * POP * args.steps / (dev_ms_max * 1e-3),
+            "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
             "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": dict(workload_config(world, "flushed between timed steps (256 MiB write); "
-                                                  "per-step CUDA events on the launching stream"),
-                           integrator={"dop853": "Dormand-Prince 8(5,3)",
-                                       "dp45": "Dormand-Prince 5(4)"}[args.method]),
-            "results_ok": ok, "nonfinite_costs": nonfinite,
-            "e2e": {"value": e2e_value, "unit": UNIT,
-                    "h2d_bytes_per_step": int(X.nbytes), "d2h_bytes_per_step": int(POP * 8),
-                    "api": "lassim_eval (C ABI) with pinned host X, host cost out"},
+            "config": workload_config(2, world),
+            "notes": {"integrator": INTEGRATORS[args.method],
+                      "l2": "every step evaluates new trial vectors (1024 x 87 doubles written by "
+                            "the trial kernel) and rewrites 2.2 MB of scratch; no flush between steps",
+                      "population": "default_rng(1000 + rank).uniform(lb, ub, (1024, 87)) on each "
+                                    "rank, evolving",
+                      "timing": "CUDA events on the engine's stream around all K steps incl. "
+                                "migrations, barrier + synchronize on both sides, max over ranks"},
+            "results_ok": bool(agree and np.isfinite(best)),
+            "e2e": {"value": e2e_total / (e2e_ms_max * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": int(POP * dim * 8), "d2h_bytes_per_step": int(POP * 8 * 4),
+                    "api": "lassim_b200.pygmo.archipelago (host-driven DE, CoreWithPerturbationsProblem"
+                           ".objfun_batch -> lassim_eval with host buffers), same migration"},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak,
-                         "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak else None,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of the evaluation's three
-                         # kernels, one ncu --set full capture (profiles/r1_m_ncu_full_summary.txt);
-                         # algorithmic bytes are X in + cost out = 0.72 MB: the path is compute-bound
-                         "traffic": 514816,
-                         "traffic_source": "profiles/r1_m_ncu_full_summary.txt (this kernel; the "
-                                           "evaluation's three kernels together: 2,266,368 bytes)",
-                         "kernel": eng.series_kernel_name(POP), "kernel_ms": d_ms,
-                         "attempts_per_launch": series_attempts,
-                         "flops_per_attempt": series_flops,
-                         "share_of_step": d_ms / k_ms,
-                         "note": "dominant kernel of the step: 2-3 limit-cycle time series of 12,000 "
-                                 "sequential attempts each set its duration (latency-bound)",
-                         # all kernels of one evaluation together (three launches, two streams)
-                         "evaluation": {"kernels": [eng.kernel_name + " (time series to the cap)",
-                                                    eng.series_kernel_name(POP),
-                                                    eng.kernel_name + " (knock-downs, second stream)"],
-                                        "ms": k_ms, "achieved": achieved_all,
-                                        "frac": achieved_all / fp64_peak if fp64_peak else None,
-                                        "step_attempts": float(np.mean(attempts)),
-                                        "explicit_pair_flops_per_attempt": flops_per_attempt},
-                         "peak_source": "in-run DFMA probe kernel (MEASURED_PEAKS.json has "
-                                        "HBM and bf16 figures only)",
-                         "machine_full": dict(sat, frac=sat["achieved_tflops"] / fp64_peak,
-                                              note="same kernel on 16 copies of the population "
-                                                   "(outside the timed region): what the kernel "
-                                                   "does when the batch outlasts its longest "
-                                                   "trajectory")},
+            "multi_gpu": {"islands": world, "individuals_per_island": POP,
+                          "generations_per_round": DE_GEN, "migrations": migrations,
+                          "migration_bytes": int(world * (dim + 1) * 8),
+                          "migration_ms": mig_max,
+                          "migration_note": "host time of de_best (waits for the island's generation) "
+                                            "+ all-reduce + upload, mean per migration, max over ranks",
+                          "collective": "torch.distributed all_reduce (NCCL) of the [islands, dim+1] "
+                                        "table of bests",
+                          "champions_agree_across_ranks": bool(agree),
+                          "best_cost": best,
+                          "ms_fastest_rank": dev_ms_min, "ms_slowest_rank": dev_ms_max},
+            "replicas": {"value": world * POP * 5 / (rep_ms * 1e-3), "ms_per_step": rep_ms / 5,
+                         "note": "diagnostic: every rank evaluates the same seed-0 population, no "
+                                 "collective (what round 1 reported as the N-GPU value)"},
+            "async_islands": dict(asy, evals_per_s_all_gpus=world * asy["islands"] * asy["individuals"]
+                                  * asy["generations"] / (asy_ms * 1e-3)),
+            "roofline": roof,
         }
-        if other is not None:
-            line["other_integrator"] = other
-        if world == 1 and not args.no_cpu_baseline:
-            arm = CpuArm(p)
-            S = sample_size(arm.cores, 32)   # about 10 s on 16 cores: includes the slow candidates
-            dt, costs = arm.run(X[:S])
-            arm.close()
-            gpu = cost_h[:S]
-            line["cpu_baseline"] = {
-                "value": S / dt, "unit": UNIT, "cores": arm.cores, "kind": arm.kind,
-                "sample": "first %d candidates of the same population, one pass, one worker "
-                          "per core (%.1f s)" % (S, dt)}
         print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+
+
+def other_config(args, ctx, config, peak, with_cpu=True):
+    """Configs 3, 4, 5 on this rank's share (strong scaling over ranks); returns a dict."""
+    from lassim_b200 import Engine
+    torch = ctx.torch
+    world, rank = ctx.world, ctx.rank
+    eng = Engine(ctx.local)
+    eng.set_method(args.method)
+    res = {"workload": CONFIG_TEXT[config]}
+    if config in (3, 4):
+        p, X = config_problem(config)
+        if config == 4 and args.c4_population:
+            X = X[:args.c4_population]
+        total = len(X)
+        X = np.ascontiguousarray(X[rank::world])
+        eng.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"], p["pert"], PERT_FACTOR)
+        eng.eval(X[:min(len(X), 64)])
+        ctx.barrier()
+        t0 = time.perf_counter()
+        r = eng.eval(X, details=True)
+        wall = time.perf_counter() - t0
+        ms = eng.last_kernel_ms()
+        ctx.barrier()
+        att = int(r["counters"][:, :2].sum())
+        steps = eng.last_traj_steps(len(X))
+        series_att = 0
+        try:
+            series_att = eng.last_stage_parallel_attempts()
+        except Exception:
+            pass
+        flops = (att - series_att) * eng.flops_per_attempt + series_att * eng.series_flops_per_attempt(len(X))
+        wall_max, ms_max = ctx.max_over_ranks([wall, ms])
+        flops_all, att_all, bad = ctx.sum_over_ranks([float(flops), float(att),
+                                                      float((r["status"] != 0).sum())])
+        res.update(candidates=total, candidates_per_gpu=len(X),
+                   trajectories_per_candidate=eng.trajectories_per_candidate,
+                   kernel=eng.kernel_name, time_series_kernel=eng.series_kernel_name(len(X)),
+                   kernel_ms=ms_max, evals_per_s=total / (ms_max * 1e-3),
+                   e2e_evals_per_s=total / wall_max, step_attempts=att_all,
+                   rejected_fraction=float(r["counters"][:, 1].sum() / max(att, 1)),
+                   longest_trajectory_attempts=int(steps.max()),
+                   achieved_tflops=flops_all / (ms_max * 1e-3) / 1e12,
+                   roofline_frac=(flops_all / (ms_max * 1e-3) / 1e12) / (peak * world) if peak else None,
+                   status_not_ok=int(bad))
+    else:
+        th2, core_x, data, sigma, y0, gene, Xp = peripheral_workload()
+        eng.set_problem(th2["data"], th2["sigma"], th2["times"], th2["y0"], th2["mask"], None, 0.0)
+        eng.set_peripheral(core_x, data, sigma, y0, None)
+        mine = (gene % world) == rank                       # gene g lives on rank g % world
+        gene_l, Xp_l = np.ascontiguousarray(gene[mine]), np.ascontiguousarray(Xp[mine])
+        eng.eval_peripheral(gene_l[:1024], Xp_l[:1024])
+        ctx.barrier()
+        t0 = time.perf_counter()
+        cost, st = eng.eval_peripheral(gene_l, Xp_l, return_status=True)
+        wall = time.perf_counter() - t0
+        ms = eng.last_kernel_ms()
+        ctx.barrier()
+        wall_max, ms_max = ctx.max_over_ranks([wall, ms])
+        bad = ctx.sum_over_ranks([float((st != 0).sum())])[0]
+        res.update(candidates=len(gene), candidates_per_gpu=len(gene_l), genes=int(gene.max()) + 1,
+                   kernel_ms=ms_max, evals_per_s=len(gene) / (ms_max * 1e-3),
+                   e2e_evals_per_s=len(gene) / wall_max, status_not_ok=int(bad),
+                   parity="unpinned: the reference has no peripheral-gene code (README.md:77-80); "
+                          "checked against oracle/lassim_oracle.py::peripheral_cost in tests/")
+    eng.close()
+    if with_cpu and rank == 0:
+        res["cpu_baseline"] = cpu_sample_other(config)
+        res["speedup_e2e_vs_cpu"] = res["e2e_evals_per_s"] / res["cpu_baseline"]["value"]
+    return res
+
+
+def run_other(args, ctx):
+    from lassim_b200 import Engine
+    peak = None
+    if ctx.rank == 0:
+        e = Engine(ctx.local)
+        peak = e.fp64_peak_tflops(400000)
+        e.close()
+    peak = ctx.max_over_ranks([peak or 0.0])[0]
+    sampler = ClockSampler(ctx.local)
+    if ctx.rank == 0:
+        sampler.start()
+    res = other_config(args, ctx, args.config, peak, with_cpu=not args.no_cpu_baseline)
+    clocks = sampler.stop() if ctx.rank == 0 else None
+    if ctx.rank == 0:
+        line = {"metric": METRIC, "value": res["evals_per_s"], "unit": UNIT, "n_gpus": ctx.world,
+                "steps": 1, "warmup": 1, "ms_per_step": res["kernel_ms"], "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": workload_config(args.config, ctx.world),
+                "e2e": {"value": res["e2e_evals_per_s"], "unit": UNIT,
+                        "api": "lassim_eval / lassim_eval_peripheral with host buffers"},
+                "clocks": clocks, "detail": res}
+        if "cpu_baseline" in res:
+            line["cpu_baseline"] = res["cpu_baseline"]
+        print(json.dumps(line), flush=True)
 
 
 def main():
@@ -417,14 +1000,27 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3, 4, 5],
+                    help="BASELINE.json config (2 = the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true")
+    ap.add_argument("--c4-population", type=int, default=0,
+                    help="config 4 with fewer than its 8192 candidates (0 = all)")
     ap.add_argument("--method", default=os.environ.get("LASSIM_METHOD", "dop853"),
                     choices=["dop853", "dp45"], help="integrator of the CUDA path")
     args = ap.parse_args()
     if args.impl == "reference":
-        run_reference_arm(args)
-    else:
-        run_ours(args)
+        return run_reference_arm(args)
+    ctx = Ctx()
+    try:
+        if args.config != 2:
+            run_other(args, ctx)
+        elif ctx.world == 1:
+            run_single(args, ctx)
+        else:
+            run_archipelago(args, ctx)
+    finally:
+        ctx.close()
 
 
 if __name__ == "__main__":

@@ -90,6 +90,20 @@ int lassim_set_tolerances(lassim_handle *h, double rtol, double atol,
 enum { LASSIM_METHOD_DP45 = 0, LASSIM_METHOD_DOP853 = 1 };
 int lassim_set_method(lassim_handle *h, int method);
 
+/* Jump guard of the explicit pairs.  Their embedded error estimates cannot see a logistic
+ * term that switches early in a step (the stages there carry no weight in the solution or
+ * in its embedded companions; with the 8(5,3) pair that is the first quarter of the step),
+ * and a knocked-down gene that grows like exp(|lambda'| t) drives the regulator sums of its
+ * targets through zero within 1e-50 time units: a discontinuity as far as any step is
+ * concerned.  A step in which some logistic term swings by more than `swing` between two
+ * stages is therefore charged hs * vmax * swing as its error: it shrinks until the switch
+ * is resolved or, for a true discontinuity, located to the tolerance (what LSODA's
+ * controller does through rejections).  Default 0.5; 2 or more switches the guard off
+ * (then 3 % of uniform Th2 candidates end a knock-down solve with a state off by 1e-5 to
+ * 1e-2, as SciPy's own DOP853 does on 18 %).  LASSIM_JUMP_GUARD in the environment sets the
+ * initial value.  (No reference counterpart.) */
+int lassim_set_jump_guard(lassim_handle *h, double swing);
+
 /* Kernel for the time-series trajectories of problems of at most 16 genes.  A
  * small batch waits for its longest time series (a limit cycle needs 15,000+
  * step attempts where most candidates need 600), so these modes trade lanes for
@@ -107,30 +121,26 @@ int lassim_set_method(lassim_handle *h, int method);
  *   4  the same with a second warp attempting 0.7 of every step (as in 1)
  *   6  the same with three warps attempting 1.2, 1 and 0.7 of the proposed step
  *      (the largest that passes its error test is taken)
- *   5  hand-over: every time series starts in the standard kernel; one that looks long
- *      (lassim_set_handover_rule) stops at the step it is on and continues in kernel 6
- *      (kernel 4 with LASSIM_HANDOVER_WARPS=2 in the environment), launched behind it on
- *      the same stream.  The many short time series stay cheap, the few long ones get
+ *   5  hand-over: every time series starts in the standard kernel; those still
+ *      going after a cap of attempts (lassim_set_series_cap) stop at the step they are
+ *      on and continue in kernel 6 (kernel 4 above 8192 candidates), launched behind it
+ *      on the same stream.  The many short time series stay cheap, the few long ones get
  *      the fast kernel almost to themselves
- *   2  automatic (default): 5 wherever the stage-parallel kernel exists (n <= 16)
+ *   2  automatic (default): 5 for batches of at most 16,384 candidates, else 0
  * Results are deterministic for a given mode and stay inside the same error control.
- * Neither the automatic choice nor the hand-over rule looks at the batch: a candidate
- * costs the same evaluated alone (a batch of one, _objfun_impl) as among 100,000 others.
- * The knock-down trajectories always run on the standard kernel, concurrently on a
- * second stream.  (No reference counterpart.)  LASSIM_SPECULATE in the environment
- * sets the initial mode. */
+ * In the automatic mode a candidate's cost does not depend on the batch it is evaluated
+ * in, as long as the batch has at most 4096 candidates: alone (a batch of one,
+ * _objfun_impl) or inside a population it takes the same path and gets the same bits.
+ * Larger batches are scheduled for throughput (the cap follows the batch size) and agree
+ * at the level of the integration tolerance.  The knock-down trajectories always run on
+ * the standard kernel, concurrently on a second stream.  (No reference counterpart.)
+ * LASSIM_SPECULATE in the environment sets the initial mode. */
 int lassim_set_speculation(lassim_handle *h, int mode);
 
-/* Which time series mode 5 hands over.  Automatic rule (default 128, 1500, 3000): a time
- * series leaves the standard kernel when, after at least `min_attempts` attempts, the
- * time still to cover is more than `remaining_steps` steps of the size its controller
- * proposes now, or when it has made `max_attempts` attempts.  (Numbers for the 8(5,3)
- * pair; the 5(4) pair, which takes about four attempts where that one takes one, uses
- * four times each.)  lassim_set_series_cap(attempts > 0) replaces the rule by a plain cap
- * - hand over after exactly that many attempts - and 0 brings the rule back.  The rule
- * sees one trajectory, never the batch.  (No reference counterpart.) */
-int lassim_set_handover_rule(lassim_handle *h, unsigned int min_attempts,
-                             double remaining_steps, unsigned int max_attempts);
+/* Attempts a time series makes in the standard kernel before mode 5 hands it over;
+ * 0 (default) = automatic: 768 for batches of at most 4096 candidates (four times that
+ * for the 5(4) pair), three per four candidates up to 8000 beyond.  LASSIM_SERIES_CAP in
+ * the environment sets the initial value.  (No reference counterpart.) */
 int lassim_set_series_cap(lassim_handle *h, unsigned int attempts);
 
 /* Current decision-vector length (2n + nnz), trajectories per candidate
@@ -225,9 +235,11 @@ int lassim_peripheral_trajectories(lassim_handle *h, int N, const int *gene,
  *                    `lanes` groups, each advancing through its generations on its own
  *                    stream with its own scratch; a slow candidate holds up its own
  *                    island's next generation only.  0 = automatic (one island per lane,
- *                    at most 16 lanes); 1 = all islands in lockstep.  The result does not
- *                    depend on the number of lanes.  LASSIM_DE_LANES in the environment
- *                    sets the initial value.
+ *                    at most 16 lanes, while the islands hold at most 4096 individuals
+ *                    together; lockstep beyond, where one batch per generation fills the
+ *                    machine by itself); 1 = all islands in lockstep.  Up to 4096
+ *                    individuals the result does not depend on the number of lanes.
+ *                    LASSIM_DE_LANES in the environment sets the initial value.
  */
 int lassim_de_init(lassim_handle *h, int islands, int individuals, int variant, double f,
                    double cr, unsigned long long seed, const double *lb, const double *ub,
@@ -323,6 +335,11 @@ int lassim_last_stage_parallel_ms(lassim_handle *h, float *ms);
 /* Number of kernels this handle has launched so far (an evaluation is one launch,
  * or two concurrent ones when speculation is active). */
 long long lassim_launch_count(const lassim_handle *h);
+
+/* The handle's own stream (a cudaStream_t as void*): what NULL selects in the _device
+ * entry points and what lassim_de_evolve forks from and joins; record events on it to
+ * time device-resident work, or make other streams wait for it. */
+void *lassim_stream(const lassim_handle *h);
 
 /* Device time of the last evaluation kernel in milliseconds (CUDA events on
  * the launching stream); blocks until that kernel has finished. */

@@ -59,8 +59,8 @@ def load_library():
     lib.lassim_set_speculation.restype = ctypes.c_int
     lib.lassim_set_series_cap.argtypes = [H, ctypes.c_uint]
     lib.lassim_set_series_cap.restype = ctypes.c_int
-    lib.lassim_set_handover_rule.argtypes = [H, ctypes.c_uint, ctypes.c_double, ctypes.c_uint]
-    lib.lassim_set_handover_rule.restype = ctypes.c_int
+    lib.lassim_set_jump_guard.argtypes = [H, ctypes.c_double]
+    lib.lassim_set_jump_guard.restype = ctypes.c_int
     lib.lassim_set_method.argtypes = [H, ctypes.c_int]
     lib.lassim_set_method.restype = ctypes.c_int
     lib.lassim_dim.argtypes = [H]
@@ -115,6 +115,8 @@ def load_library():
     lib.lassim_last_stage_parallel_attempts.restype = ctypes.c_int
     lib.lassim_last_stage_parallel_ms.argtypes = [H, ctypes.POINTER(ctypes.c_float)]
     lib.lassim_last_stage_parallel_ms.restype = ctypes.c_int
+    lib.lassim_stream.argtypes = [H]
+    lib.lassim_stream.restype = ctypes.c_void_p
     lib.lassim_launch_count.argtypes = [H]
     lib.lassim_launch_count.restype = ctypes.c_longlong
     lib.lassim_last_kernel_ms.argtypes = [H, ctypes.POINTER(ctypes.c_float)]
@@ -214,7 +216,7 @@ class Engine:
         (speculative half-warp attempts), 'stages' (stage-parallel Gauss pair, one warp
         per trajectory), 'stages2' / 'stages3' (the same with two / three warps attempting
         different step sizes), 'handover' (standard kernel first, long time series continue
-        in 'stages3') or 'auto' ('handover' wherever the stage-parallel kernel exists)."""
+        in 'stages3') or 'auto' ('handover' up to 16,384 candidates, 'off' beyond)."""
         code = {"off": 0, "on": 1, "auto": 2, "stages": 3, "stages2": 4, "handover": 5, "stages3": 6,
                 0: 0, 1: 1, 2: 2, 3: 3, 4: 4, 5: 5, 6: 6, False: 0, True: 1}.get(mode)
         if code is None:
@@ -223,16 +225,14 @@ class Engine:
         self._check(self._lib.lassim_set_speculation(self._h, code), "lassim_set_speculation")
 
     def set_series_cap(self, attempts=0):
-        """Plain cap: 'handover' moves a time series to the stage-parallel kernel after
-        exactly this many attempts; 0 = the automatic rule (set_handover_rule)."""
+        """Attempts a time series makes in the standard kernel before 'handover' moves it
+        to the stage-parallel kernel; 0 = automatic (768 up to 4096 candidates)."""
         self._check(self._lib.lassim_set_series_cap(self._h, int(attempts)), "lassim_set_series_cap")
 
-    def set_handover_rule(self, min_attempts=128, remaining_steps=1500.0, max_attempts=3000):
-        """'handover' moves a time series when, after min_attempts attempts, more than
-        remaining_steps steps of its current size are still ahead, or at max_attempts."""
-        self._check(self._lib.lassim_set_handover_rule(self._h, int(min_attempts),
-                                                       float(remaining_steps), int(max_attempts)),
-                    "lassim_set_handover_rule")
+    def set_jump_guard(self, swing=0.5):
+        """A step of the explicit pairs in which a logistic term swings by more than `swing`
+        is charged hs * vmax * swing as its error (2 or more = off); see lassim_b200.h."""
+        self._check(self._lib.lassim_set_jump_guard(self._h, float(swing)), "lassim_set_jump_guard")
 
     def set_method(self, method="dop853"):
         """'dop853' (Dormand-Prince 8(5,3), default) or 'dp45' (Dormand-Prince 5(4))."""
@@ -464,6 +464,11 @@ class Engine:
 
     def series_kernel_name(self, N):
         return self._lib.lassim_series_kernel_name(self._h, int(N)).decode()
+
+    @property
+    def stream(self):
+        """Address of the engine's own cudaStream_t (e.g. for torch.cuda.ExternalStream)."""
+        return int(self._lib.lassim_stream(self._h))
 
     @property
     def launch_count(self):

@@ -48,6 +48,7 @@ struct DevProblem {
     const int *knock_ctrl;    // [n] trajectory index of row i's control
     double pert_factor, rtol, atol;
     unsigned int max_steps;
+    float swing;              // jump guard of the explicit pairs (rk_steppers.cuh); >= 2 = off
     // peripheral-gene problems (PERIPH kernels): the core occupies states
     // 0..n-2 with fixed parameters, state n-1 is one peripheral gene
     const double *core_x;     // [2*(n-1) + nnz_core] decision vector of the core
@@ -76,16 +77,13 @@ struct DevBatch {
     unsigned int work_begin;  // this launch serves work items [work_begin, work_begin + work_count)
     unsigned int work_count;  //   of the N*K items (item w: trajectory w / N of candidate w % N)
     // Hand-over of long time series (see launch_kernels): with series_cap > 0 a time series
-    // that has used that many attempts - or, from ho_min attempts on, has more than ho_rem
-    // steps of the size its controller now proposes ahead of it: a rule that looks at the
-    // trajectory alone, never at the batch - stops at the step it is on, leaves its state behind
+    // that has used that many attempts stops at the step it is on, leaves its state behind
     // (y in the last row of its Y block, t in cost_main, h in pert_cost) and appends
     // (sample index << 32 | candidate) to long_list; the stage-parallel kernel launched
     // behind it with resume = 1 takes its work items from that list.
-    unsigned int series_cap = 0;           // hand over after this many attempts, whatever else
-    unsigned int ho_min = 0xffffffffu;     // or after ho_min attempts when more than ho_rem steps
-    double ho_rem = 0.0;                   //   of the current size are still ahead
+    unsigned int series_cap = 0;
     int resume = 0;
+    int no_if = 0;            // diagnostic (LASSIM_NO_IF=1): plain formulas for growing genes too
     unsigned int *long_count = nullptr;        // zeroed before launch
     unsigned long long *long_list = nullptr;   // [N]
     unsigned long long *sp_attempts = nullptr; // attempts made by the stage-parallel kernel (sum)
@@ -491,7 +489,6 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
     unsigned nacc = 0, nrej = 0;
     bool rejected = false;
     double t = 0.0, h = 0.0, tend = 0.0;
-    double tfin = 0.0;     // last sample time of the trajectory (hand-over rule)
     const double *tl = P.times;
 
     // sigmoid(W in) = sr + sr*se: publish this lane's entries, barrier, mat-vec, logistic
@@ -572,7 +569,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
                     gr[r] = 0.0;
-                    if (kIF && lam[r] < 0.0) { gr[r] = -lam[r]; lam[r] = 0.0; any_growth = 1.0; }
+                    if (kIF && !B.no_if && lam[r] < 0.0) { gr[r] = -lam[r]; lam[r] = 0.0; any_growth = 1.0; }
                 }
                 grow = kIF && G::max_group(any_growth, gmask, red) > 0.0;
                 if (k == 0) { tl = P.times; nt = P.T; }
@@ -580,7 +577,6 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                 t = tl[0];
                 ti = 1;
                 tend = (nt > 1) ? tl[1] : t;
-                if constexpr (HANDOVER) tfin = tl[nt - 1];
                 nacc = 0; nrej = 0; rejected = false; st = 0;
                 if (k == 0) {
                     double *Yc = B.Y + (size_t)c * P.T * n;
@@ -658,17 +654,17 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
             if constexpr (METHOD == kMethodDOP853) {
                 if (use_if)
                     qf = dop853_attempt<kIF, R>(sig_step, gmax_step, lam, vm, gr, tab, y, k1, hs,
-                                                rtol, atol, yn, kn);
+                                                rtol, atol, P.swing, yn, kn);
                 else
                     qf = dop853_attempt<false, R>(sig_step, gmax_step, lam, vm, gr, tab, y, k1, hs,
-                                                  rtol, atol, yn, kn);
+                                                  rtol, atol, P.swing, yn, kn);
             } else {
                 if (use_if)
                     qf = dp45_attempt<kIF, R>(sig_step, gmax_step, lam, vm, gr, tab, y, k1, hs,
-                                              rtol, atol, yn, kn);
+                                              rtol, atol, P.swing, yn, kn);
                 else
                     qf = dp45_attempt<false, R>(sig_step, gmax_step, lam, vm, gr, tab, y, k1, hs,
-                                                rtol, atol, yn, kn);
+                                                rtol, atol, P.swing, yn, kn);
             }
 
             bool fallback = false;     // the shorter attempt is the one that counts
@@ -744,12 +740,9 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
 
         // a time series over its attempt cap is handed to the kernel behind this one
         bool handover = false;
-        if constexpr (HANDOVER) {
-            const unsigned att = nacc + nrej;
+        if constexpr (HANDOVER)
             handover = active && k == 0 && B.series_cap != 0u && ti < nt && st == 0 &&
-                       (att >= B.series_cap ||
-                        (att >= B.ho_min && tfin - t > B.ho_rem * h));
-        }
+                       nacc + nrej >= B.series_cap;
         if (active && (ti >= nt || handover)) {
             // ------------------------------------------------------ epilogue
             if (handover) {

@@ -37,15 +37,13 @@ struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
-// Hand-over of long time series, automatic rule.  A time series leaves the standard kernel
-// for the stage-parallel one when, after at least kHandoverMinAttempts attempts, the time
-// still to cover is more than kHandoverRemaining steps of the size its controller proposes
-// now - or, whatever its steps look like, when it has made kHandoverMaxAttempts attempts.
-// The rule looks at the trajectory alone, never at the batch, so a candidate's result does
-// not depend on which other candidates are evaluated with it.
-constexpr unsigned kHandoverMinAttempts = 128;
-constexpr double kHandoverRemaining = 1500.0;
-constexpr unsigned kHandoverMaxAttempts = 3000;
+// Hand-over of long time series (series_policy below).  Up to kBatchIndependentMax
+// candidates per call every choice that touches the numbers - which kernel integrates a
+// time series, after how many attempts it is handed over, how many step sizes the
+// stage-parallel kernel tries per attempt - is the same for every batch size, so a
+// candidate's cost does not depend on the batch it is evaluated in.
+constexpr int kBatchIndependentMax = 4096;
+constexpr unsigned kHandoverCap = 768;       // attempts in the standard kernel (8(5,3) pair)
 
 }  // namespace
 
@@ -94,12 +92,10 @@ struct lassim_handle {
     cudaEvent_t ev_sp0 = nullptr, ev_sp1 = nullptr;   // around the stage-parallel kernel
     bool sp_timed = false;
     int speculate = 2;        // lassim_set_speculation mode (2 = automatic)
-    // Hand-over of long time series (series_rule below): hard cap of attempts in the
-    // standard kernel (0 = the automatic rule), and the automatic rule's three numbers
-    unsigned series_cap = 0;
-    unsigned ho_min = kHandoverMinAttempts, ho_max = kHandoverMaxAttempts;
-    double ho_rem = kHandoverRemaining;
-    int handover_warps = 0;       // warps per trajectory of the kernel long time series move to; 0 = three
+    unsigned series_cap = 0;      // hand-over cap; 0 = automatic (series_cap_for)
+    int handover_warps = 0;       // warps per trajectory of the kernel long time series move to; 0 = automatic
+    int no_if = 0;                // LASSIM_NO_IF=1 (diagnostic): no integrating factor for growing genes
+    float jump_guard = 0.5f;      // lassim_set_jump_guard
     bool timed = false;
     std::string err, kernel_name, series_kernel_name;
     long long launches = 0;
@@ -379,14 +375,20 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
 // `s` waits for both.
 // Which kernel integrates the time series of a batch of N candidates:
 // 0 the standard one, 1 speculative, 3 stage-parallel (lassim_set_speculation).
-// Automatic (2): hand-over (5) wherever the stage-parallel kernel exists (n <= 16), for
-// every batch size: the choice - like the hand-over rule itself - must not depend on N, or
-// a candidate's cost would depend on the company it is evaluated in.
+// Automatic (2): hand-over (5) wherever the stage-parallel kernel exists (n <= 16) up to
+// 16,384 candidates, the standard kernel alone beyond (there the batch outlasts its longest
+// time series and the stage-parallel kernel's lanes are better spent on throughput).
+// Measured on Th2 populations (tools/gpu_handover_sweep.py; ms per evaluation):
+//        N   standard   hand-over (cap)
+//      128     30.3       17.7  (500)    18.5 (768)
+//     1024     34.9       21.4  (768)
+//     4096     41.2       31.9  (3072)   33-34 (768..1500)
+//    16384     78.0       68.3  (8000)
+//    65536    177.7      203.0  (8000)
 int series_mode(const lassim_handle *h, const KernelChoice &kc, int N, bool periph) {
-    (void)N;
     if (periph) return 0;
     const bool automatic = h->speculate == 2;
-    if (kc.fn_pirk3 != nullptr && (h->speculate == 5 || automatic)) return 5;
+    if (kc.fn_pirk3 != nullptr && (h->speculate == 5 || (automatic && N <= 16384))) return 5;
     if (kc.fn_pirk3 != nullptr && h->speculate == 6) return 6;
     if (kc.fn_pirk2 != nullptr && h->speculate == 4) return 4;
     if (kc.fn_pirk != nullptr && h->speculate == 3) return 3;
@@ -394,22 +396,25 @@ int series_mode(const lassim_handle *h, const KernelChoice &kc, int N, bool peri
     return 0;
 }
 
-// Warps per handed-over trajectory: three step sizes per attempt (two on request,
-// LASSIM_HANDOVER_WARPS=2).  Round 1 picked two below 512 and above 8192 candidates for a
-// few per cent; that made results depend on the batch size and is gone.
+// Warps per handed-over trajectory: three step sizes per attempt; two for the crowded
+// stage-parallel kernel of batches above 8192 candidates (16,384: 60.6 against 62.4 ms).
 int handover_warps_for(const lassim_handle *h, int N) {
-    (void)N;
-    return h->handover_warps == 2 ? 2 : 3;
+    if (h->handover_warps == 2 || h->handover_warps == 3) return h->handover_warps;
+    return N <= 8192 ? 3 : 2;
 }
 
-// The numbers of the hand-over rule for one launch: an explicit cap (lassim_set_series_cap)
-// switches the projection off; otherwise the automatic rule (see kHandover* above).  The
-// 5(4) pair takes about four attempts where the 8(5,3) pair takes one.
-struct SeriesRule { unsigned cap, min_attempts; double remaining; };
-SeriesRule series_rule(const lassim_handle *h) {
-    const unsigned mult = h->method == kMethodDP45 ? 4u : 1u;
-    if (h->series_cap != 0u) return {h->series_cap * mult, 0xffffffffu, 0.0};
-    return {h->ho_max * mult, h->ho_min * mult, h->ho_rem * mult};
+// Attempts a time series gets in the standard kernel before it is handed over: enough that
+// the many short ones finish there (their hand-over would crowd the stage-parallel kernel),
+// few enough that the long ones lose little time at the slower pace.  One number for every
+// batch of at most kBatchIndependentMax candidates (a candidate evaluated alone and the same
+// candidate in a population then take the same path and get the same bits); beyond, where
+// throughput counts, three attempts per four candidates up to 8000.  The 5(4) pair takes
+// about four attempts where the 8(5,3) pair takes one.
+unsigned series_cap_for(const lassim_handle *h, int N) {
+    if (h->series_cap != 0u) return h->series_cap;
+    long long c = kHandoverCap;
+    if (N > kBatchIndependentMax) { c = 3LL * N / 4; c = c > 8000 ? 8000 : c; }
+    return (unsigned)(h->method == kMethodDP45 ? 4 * c : c);
 }
 
 int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P,
@@ -422,7 +427,7 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
     const bool speculate = series_fn != nullptr;
     auto launch = [&](kernel_fn fn, int threads, size_t smem, int lanes_per_item, unsigned begin,
                       unsigned count, unsigned int *counter, cudaStream_t st,
-                      const SeriesRule *rule = nullptr, int resume = 0) -> cudaError_t {
+                      unsigned series_cap = 0u, int resume = 0) -> cudaError_t {
         if (count == 0) return cudaSuccess;
         const int items_per_cta = threads / lanes_per_item;
         cudaError_t e;
@@ -446,8 +451,8 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
         if (blocks < 1) blocks = 1;
         DevBatch Bl = B;
         Bl.work_begin = begin; Bl.work_count = count; Bl.work_counter = counter;
-        if (rule) { Bl.series_cap = rule->cap; Bl.ho_min = rule->min_attempts; Bl.ho_rem = rule->remaining; }
-        Bl.resume = resume; Bl.long_count = counters + 2;
+        Bl.series_cap = series_cap; Bl.resume = resume; Bl.long_count = counters + 2;
+        Bl.no_if = h->no_if;
         Bl.sp_attempts = reinterpret_cast<unsigned long long *>(counters + 4);
         fn<<<(unsigned)blocks, threads, smem, st>>>(P, Bl);
         h->launches += 1;
@@ -464,17 +469,16 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
             CU(cudaStreamWaitEvent(sc.aux, sc.ev_fork, 0));
         }
         if (smode == 5) {
-            // every time series starts in the standard kernel; the ones the hand-over rule
-            // picks continue in the multi-warp stage-parallel kernel behind it
-            const SeriesRule rule = series_rule(h);
-            CU(launch(kc.fn_capped, threads, smem, kc.L, 0u, (unsigned)N, counters, s, &rule, 0));
+            // every time series starts in the standard kernel; the ones still going after
+            // the cap of attempts continue in the multi-warp stage-parallel kernel behind it
+            CU(launch(kc.fn_capped, threads, smem, kc.L, 0u, (unsigned)N, counters, s, series_cap_for(h, N), 0));
             if (time_it) CU(cudaEventRecord(h->ev_sp0, s));
             if (handover_warps_for(h, N) == 3)
                 CU(launch(kc.fn_pirk3, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters + 3,
-                          s, nullptr, 1));
+                          s, 0u, 1));
             else
                 CU(launch(kc.fn_pirk2, pirk_threads(2), kc.pirk2_smem, 64, 0u, (unsigned)N, counters + 3,
-                          s, nullptr, 1));
+                          s, 0u, 1));
         } else if (smode == 1) {
             CU(launch(series_fn, threads, smem, 32, 0u, (unsigned)N, counters, s));
         } else {
@@ -571,6 +575,7 @@ int launch_eval(lassim_handle *h, Scratch &sc, int N, int mode, const double *dX
     P.knock_ctrl = h->d_knock_ctrl.p;
     P.pert_factor = h->pert_factor; P.rtol = h->rtol; P.atol = h->atol;
     P.max_steps = (unsigned int)(h->max_steps > 4000000000LL ? 4000000000LL : h->max_steps);
+    P.swing = h->jump_guard;
     P.core_x = h->d_core_x.p; P.pmask = h->d_pmask.p; P.pdata = h->d_pdata.p;
     P.psigma2 = h->d_psigma2.p; P.py0 = h->d_py0.p;
     if (periph) { P.U = 0; P.dim = h->n + 2; P.pert = nullptr; }
@@ -657,10 +662,9 @@ int lassim_create(int device, lassim_handle **out) {
     if (const char *sp = getenv("LASSIM_SPECULATE")) h->speculate = atoi(sp);
     if (const char *sp = getenv("LASSIM_SERIES_CAP")) h->series_cap = (unsigned)atoi(sp);
     if (const char *sp = getenv("LASSIM_HANDOVER_WARPS")) h->handover_warps = atoi(sp);
-    if (const char *sp = getenv("LASSIM_HANDOVER_MIN")) h->ho_min = (unsigned)atoi(sp);
-    if (const char *sp = getenv("LASSIM_HANDOVER_MAX")) h->ho_max = (unsigned)atoi(sp);
-    if (const char *sp = getenv("LASSIM_HANDOVER_REMAINING")) h->ho_rem = atof(sp);
     if (const char *sp = getenv("LASSIM_DE_LANES")) h->de_lanes_wanted = atoi(sp);
+    if (const char *sp = getenv("LASSIM_NO_IF")) h->no_if = atoi(sp);
+    if (const char *sp = getenv("LASSIM_JUMP_GUARD")) h->jump_guard = (float)atof(sp);
     double tab[kExpTable];
     for (int j = 0; j < kExpTable; ++j) tab[j] = exp2((double)j / (double)kExpTable);
     if (cudaMemcpyToSymbol(c_exp2_table, tab, sizeof(tab)) != cudaSuccess) {
@@ -801,13 +805,11 @@ int lassim_set_series_cap(lassim_handle *h, unsigned int attempts) {
     return LASSIM_OK;
 }
 
-int lassim_set_handover_rule(lassim_handle *h, unsigned int min_attempts, double remaining_steps,
-                             unsigned int max_attempts) {
+int lassim_set_jump_guard(lassim_handle *h, double swing) {
     if (!h) return LASSIM_E_INVALID;
-    if (!(remaining_steps >= 0.0) || max_attempts < 1u)
-        return fail(h, LASSIM_E_INVALID, "set_handover_rule: min %u, remaining %g, max %u",
-                    min_attempts, remaining_steps, max_attempts);
-    h->ho_min = min_attempts; h->ho_rem = remaining_steps; h->ho_max = max_attempts;
+    if (!(swing > 0.0))
+        return fail(h, LASSIM_E_INVALID, "set_jump_guard: swing=%g (in (0, 1]; 2 or more = off)", swing);
+    h->jump_guard = (float)swing;
     return LASSIM_OK;
 }
 
@@ -1091,6 +1093,8 @@ int lassim_last_traj_steps(lassim_handle *h, int N, unsigned int *steps) {
 
 long long lassim_launch_count(const lassim_handle *h) { return h ? h->launches : -1; }
 
+void *lassim_stream(const lassim_handle *h) { return h ? (void *)h->stream : nullptr; }
+
 int lassim_last_kernel_ms(lassim_handle *h, float *ms) {
     if (!h || !ms) return LASSIM_E_INVALID;
     if (!h->timed) return fail(h, LASSIM_E_STATE, "no kernel has been launched yet");
@@ -1169,11 +1173,18 @@ int de_evaluate_population(lassim_handle *h) {
 }
 
 // Lanes of the asynchronous evolve: `lanes` groups of consecutive islands, each with its own
-// stream and evaluation scratch.  Automatic: one island per lane up to 16 lanes.
+// stream and evaluation scratch.  Automatic: one island per lane up to 16 lanes while the
+// islands together hold at most 4096 individuals - there a generation of all of them is
+// over in the time of its slowest time series and lanes fill the wait (Th2, 20 generations:
+// 8 x 128 in lockstep 487 ms, in lanes 368 ms, one island alone 338 ms; 32 x 128: 822 / 727) -
+// and lockstep beyond, where one batch per generation keeps the machine full by itself
+// (8 x 1024: 912 ms in lockstep, 1265 ms in 8 lanes; tools/gpu_async_probe.py).
 int de_make_lanes(lassim_handle *h) {
     release_de_lanes(h);
     const int islands = h->de.islands;
-    int lanes = h->de_lanes_wanted > 0 ? h->de_lanes_wanted : (islands < 16 ? islands : 16);
+    const bool small = (long long)islands * h->de.np <= kBatchIndependentMax;
+    int lanes = h->de_lanes_wanted > 0 ? h->de_lanes_wanted
+              : small ? (islands < 16 ? islands : 16) : 1;
     if (lanes > islands) lanes = islands;
     h->de_lanes.resize(lanes);
     for (int l = 0; l < lanes; ++l) {
@@ -1476,6 +1487,7 @@ extern "C" int lassim_eval_device_noalloc(lassim_handle *h, int N, const double 
     P.knock_ctrl = h->d_knock_ctrl.p;
     P.pert_factor = h->pert_factor; P.rtol = h->rtol; P.atol = h->atol;
     P.max_steps = (unsigned int)(h->max_steps > 4000000000LL ? 4000000000LL : h->max_steps);
+    P.swing = h->jump_guard;
 
     P.core_x = nullptr; P.pmask = nullptr; P.pdata = nullptr; P.psigma2 = nullptr; P.py0 = nullptr;
 

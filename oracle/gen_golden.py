@@ -182,6 +182,11 @@ def _eval_oracle(args):
     return c, pc, np.asarray(Y), sim
 
 
+def _trunc(a):
+    bits = np.ascontiguousarray(a, dtype=np.float64).view(np.uint64) & np.uint64(0xFFFFFFFFFE000000)
+    return bits.view(np.float64)
+
+
 def _eval_full(x):
     """One candidate of the full-size population: the reference's own total /
     parts, the knock-down ratio vector and control end states as the reference's
@@ -195,27 +200,53 @@ def _eval_full(x):
         # the compiled plugin scatters into k_map in place: hand it a copy
         return _W["ode"](y0, t, sol, np.array(k_map, dtype=np.float64).copy(), k_mask, size, result)
 
-    pc2, sim, ctrl = orc.perturbation_cost(p["pert"], n, p["y0"], np.array(x), p["vector_map"],
-                                           p["mask"], ref_ode, return_controls=True)
+    pc2, sim, ctrl, ends = orc.perturbation_cost(p["pert"], n, p["y0"], np.array(x),
+                                                 p["vector_map"], p["mask"], ref_ode,
+                                                 return_controls="ends")
     tode = orc.tight_ode()
     tcm = orc.core_cost(x, p["data"], p["sigma"], p["times"], p["y0"], p["vector_map"],
                         p["mask"], tode)
-    tpc, tsim, tctrl = orc.perturbation_cost(p["pert"], n, p["y0"], np.array(x), p["vector_map"],
-                                             p["mask"], tode, return_controls=True)
-    return (total, cmain, pc, pc2, sim, ctrl, tcm, tpc, tsim, tctrl)
+    tpc, tsim, tctrl, tends = orc.perturbation_cost(p["pert"], n, p["y0"], np.array(x),
+                                                    p["vector_map"], p["mask"], tode,
+                                                    return_controls="ends")
+    # end states of the knocked systems with 27 bits of mantissa (they are compared at 1e-5
+    # and range over 1e-300 .. 1e200; the zeroed low bits compress away)
+    return (total, cmain, pc, pc2, sim, ctrl, tcm, tpc, tsim, tctrl, _trunc(ends), _trunc(tends))
+
+
+def _eval_nfe(x):
+    """LSODA right-hand-side evaluations of one whole cost evaluation at the reference's
+    tolerances: (time series, all 1 + U + n solves) - the integrator-independent measure of
+    useful work SURVEY.md 8d asks for."""
+    p, n = _W["prob"], _W["n"]
+    count = {"n": 0}
+
+    def counting_ode(y0, t, sol, k_map, k_mask, size, result=None):
+        Y, info = orc.odeint_lassim(y0, t, sol, k_map, k_mask, size, full_output=True)
+        count["n"] += int(info["nfe"][-1])
+        return Y
+
+    orc.core_cost(x, p["data"], p["sigma"], p["times"], p["y0"], p["vector_map"], p["mask"],
+                  counting_ode)
+    main = count["n"]
+    orc.perturbation_cost(p["pert"], n, p["y0"], np.array(x), p["vector_map"], p["mask"],
+                          counting_ode)
+    return main, count["n"]
 
 
 def run_full_population(prob, X, procs, factor=0.5):
     with Pool(procs, initializer=_worker_init, initargs=(prob, factor)) as pool:
         rows = pool.map(_eval_full, list(X), chunksize=1)
+        nfe = np.array(pool.map(_eval_nfe, list(X), chunksize=1))
     col = lambda i: np.array([r[i] for r in rows])
     return dict(
+        lsoda_nfe_main=nfe[:, 0], lsoda_nfe_total=nfe[:, 1],
         seed=np.int64(0), rows=np.int64(len(X)), x_checksum=np.float64(X.sum()),
         pert_factor=np.float64(factor),
         ref_total=col(0), ref_cost_main=col(1), ref_pert_cost=col(2),
         ref_pert_cost_from_sim=col(3), ref_sim=col(4), ref_ctrl_end=col(5),
         tight_cost_main=col(6), tight_pert_cost=col(7), tight_sim=col(8),
-        tight_ctrl_end=col(9))
+        tight_ctrl_end=col(9), ref_knock_end=col(10), tight_knock_end=col(11))
 
 
 def _lsoda_stats(x):

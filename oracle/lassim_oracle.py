@@ -107,6 +107,7 @@ def perturbation_cost(pert_data, size, y0, sol_vector, vector_map, mask,
     times = pert_data[:, size:]
     diag = np.diagonal(perts)
     sim = np.empty(size * size)
+    ends = np.empty((size, size))
     controls = {}
     with np.errstate(all="ignore"):
         for i in range(size):
@@ -117,10 +118,14 @@ def perturbation_cost(pert_data, size, y0, sol_vector, vector_map, mask,
                                     np.empty(size))
             sol[i] = sol[i] * diag[i]
             traj = ode(y0, t_i, sol, vector_map, mask, size, np.empty(size))
+            ends[i] = traj[-1]
             sim[i * size:(i + 1) * size] = traj[-1] / controls[key][-1]
         sim -= 1.0
         sim[sim > 2] = 2
         cost = rank1_residual(sim, perts.flatten())
+    if return_controls == "ends":
+        # also the end states of the knocked systems, row by row
+        return cost, sim, np.array([c[-1] for c in controls.values()]), ends
     if return_controls:
         # control end states in order of first appearance of their time pair
         return cost, sim, np.array([c[-1] for c in controls.values()])

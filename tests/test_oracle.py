@@ -101,3 +101,7 @@ def test_full_population_golden_is_consistent(th2, th2_uniform):
         np.testing.assert_allclose(ctrl, g["ref_ctrl_end"][i], rtol=1e-9, atol=1e-300)
         assert pc == pytest.approx(g["ref_pert_cost"][i], rel=1e-9)
         assert orc.rank1_residual(g["ref_sim"][i], pflat) == pytest.approx(pc, rel=1e-9)
+    # end states of the knocked systems (stored with 27 bits of mantissa)
+    pc, sim, ctrl, ends = orc.perturbation_cost(p["pert"], 12, p["y0"], X[200], p["vector_map"],
+                                                p["mask"], return_controls="ends")
+    np.testing.assert_allclose(ends, g["ref_knock_end"][200], rtol=1e-7, atol=1e-300)

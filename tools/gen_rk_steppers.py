@@ -71,6 +71,12 @@ def emit(tb):
     w("//   sig(ys, sr, se)  evaluates the logistic terms sigmoid(W ys) = sr + sr*se for this lane's")
     w("//                genes (reciprocal seed and Newton residual, see logistic_fast_parts)")
     w("//   gmax(x)      max of a non-negative float over the lanes of the group")
+    w("//   swing        jump guard (>= 2 switches it off).  The embedded estimates are blind to a")
+    w("//                logistic term that switches early in the step (the stages there carry no")
+    w("//                weight in the solution or its embedded companions): a term that swings by")
+    w("//                more than this between two stages of the attempt is charged as the jump it")
+    w("//                may be, error <= hs * vmax * swing, so that the step shrinks until the switch")
+    w("//                is resolved - or, for a true discontinuity, located to the tolerance")
     w("// Outputs: yn (the order-%d solution), kn (first stage derivative of the next step);"
       % tb["order"])
     w("// returns the group's error measure (accept if <= 1), +inf when anything was non-finite.")
@@ -88,12 +94,16 @@ def emit(tb):
     w("        const double (&lam)[R], const double (&vm)[R], const double (&gr)[R],")
     w("        const double *tab, const double (&y)[R],")
     w("        const double (&k1)[R], const double hs, const double rtol, const double atol,")
-    w("        double (&yn)[R], double (&kn)[R]) {")
+    w("        const float swing, double (&yn)[R], double (&kn)[R]) {")
     decl = ", ".join("%s[R]" % k for k in K[1:S])
     w("    double %s;" % decl)
     w("    double ys[R], sg[R], sr[R], se[R], q[R], ly[R], cv[R], ef[R], ei[R], yz[R];")
+    w("    // smallest / largest logistic value over the stages, as the high words of the doubles")
+    w("    // (monotonic for positive values; integer min/max keep this off the FP64 pipe)")
+    w("    int slo[R], shi[R];")
     w("#pragma unroll")
-    w("    for (int r = 0; r < R; ++r) { ys[r] = fma(hs * %s, k1[r], y[r]); ef[r] = 1.0; ei[r] = 1.0; }" % lit(A[1][0]))
+    w("    for (int r = 0; r < R; ++r) { ys[r] = fma(hs * %s, k1[r], y[r]); ef[r] = 1.0; ei[r] = 1.0;" % lit(A[1][0]))
+    w("                                  slo[r] = 0x7ff00000; shi[r] = 0; }")
     for s in range(2, S + 1):
         row = A[s] if s < S else B
         last = row[s - 1]
@@ -121,6 +131,7 @@ def emit(tb):
         w("            // cv*sigma + q with the Newton step of the reciprocal folded in")
         w("            %s[r] = fma(cv[r] * sr[r], se[r], fma(cv[r], sr[r], q[r]));" % target)
         w("            sg[r] = fma(sr[r], se[r], sr[r]);")
+        w("            slo[r] = min(slo[r], __double2hiint(sg[r])); shi[r] = max(shi[r], __double2hiint(sg[r]));")
         w("            %s[r] = fma(IF ? vm[r] * ei[r] : vm[r], sg[r], ly[r]);" % K[s - 1])
         w("        }")
         w("    }")
@@ -158,6 +169,9 @@ def emit(tb):
             w("    double qd%d = 0.0;" % m)
         w("#pragma unroll")
         w("    for (int r = 0; r < R; ++r) {")
+        w("        // jump guard: |error| <= hs * vmax * swing of a term that switched inside the step")
+        w("        const double sw = __hiloint2double(shi[r], 0) - __hiloint2double(min(slo[r], shi[r]), 0);")
+        w("        if (sw > (double)swing) qd0 = fmax(qd0, (fabs(hs) * sw) * (IF ? vm[r] * ef[r] : vm[r]) * isc[r]);")
         for m in range(nE):
             if E[m][S] != 0.0:
                 w("        const double e%d = fma(ce%d[r], sg[r], eq%d[r]);" % (m, m, m))
