@@ -5,6 +5,7 @@
 #include "../../include/lassim_b200.h"
 #include "grn_kernels.cuh"
 #include "pirk_kernel.cuh"
+#include "pirk_wide_kernel.cuh"
 #include "de_kernels.cuh"
 
 #include <cmath>
@@ -233,6 +234,9 @@ struct KernelChoice {
     kernel_fn fn_pirk3 = nullptr;    // three warps, three step sizes
     size_t pirk3_smem = 0;
     kernel_fn fn_capped = nullptr;   // fn with the hand-over cap compiled in
+    kernel_fn fn_wide = nullptr;     // CTA-per-trajectory stage-parallel kernel (17 .. 64 genes)
+    int wide_threads = 0;
+    size_t wide_smem = 0;
 };
 
 // dynamic shared memory of one CTA: header (2^(j/256) table, reduction scratch)
@@ -281,6 +285,34 @@ void pirk_kernel(int n, KernelChoice *out) {
         out->fn_pirk3 = grn_series_pirk_kernel<4, 8, 16, true, 3>;
         out->pirk3_smem = pirk_smem_doubles(4, 8, 16, 3) * sizeof(double);
     }
+}
+
+// the 17 .. 64-gene kernels with the hand-over cap compiled in, and the stage-parallel kernel
+// their long time series continue in (5 Gauss stages x 32 or 64 lanes)
+template <int NC>
+void wide_dense(int method, KernelChoice *out) {
+    out->fn_capped = method == kMethodDOP853
+        ? grn_cost_kernel<32, 1, DenseW<1, NC>, kMethodDOP853, true, false, false, true>
+        : grn_cost_kernel<32, 1, DenseW<1, NC>, kMethodDP45, true, false, false, true>;
+    out->fn_wide = grn_series_pirk_wide_kernel<5, 1, DenseW<1, NC>, true>;
+    out->wide_threads = pirk_wide_threads(5, 1);
+    out->wide_smem = pirk_wide_smem_doubles(5, 1) * sizeof(double);
+}
+
+void wide_sparse(int method, int max_deg, KernelChoice *out) {
+    if (max_deg <= 8) {
+        out->fn_capped = method == kMethodDOP853
+            ? grn_cost_kernel<64, 1, EllW<1, 8>, kMethodDOP853, true, false, false, true>
+            : grn_cost_kernel<64, 1, EllW<1, 8>, kMethodDP45, true, false, false, true>;
+        out->fn_wide = grn_series_pirk_wide_kernel<5, 2, EllW<1, 8>, true>;
+    } else {
+        out->fn_capped = method == kMethodDOP853
+            ? grn_cost_kernel<64, 1, CsrW<1>, kMethodDOP853, true, false, false, true>
+            : grn_cost_kernel<64, 1, CsrW<1>, kMethodDP45, true, false, false, true>;
+        out->fn_wide = grn_series_pirk_wide_kernel<5, 2, CsrW<1>, true>;
+    }
+    out->wide_threads = pirk_wide_threads(5, 2);
+    out->wide_smem = pirk_wide_smem_doubles(5, 2) * sizeof(double);
 }
 
 template <int L, int R>
@@ -337,6 +369,7 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
         kernel_fn fn = nc <= 24 ? dense_kernel<32, 24>(method, fast)
                                 : dense_kernel<32, 32>(method, fast);
         *out = {fn, 32, 1, "dense 32x1"};
+        if (fast) { if (nc <= 24) wide_dense<24>(method, out); else wide_dense<32>(method, out); }
         return true;
     }
     // 33..64 genes: one gene per lane, a CTA of 64 threads per trajectory.  With two genes per
@@ -348,7 +381,10 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
     const char *r2 = getenv("LASSIM_SPARSE_R2");
     if (n <= 64) {
         if (r2 && atoi(r2) != 0) *out = {sparse_kernel<32, 2>(method, h->max_deg), 32, 2, "sparse 32x2"};
-        else *out = {sparse_kernel<64, 1>(method, h->max_deg), 64, 1, "sparse 64x1"};
+        else {
+            *out = {sparse_kernel<64, 1>(method, h->max_deg), 64, 1, "sparse 64x1"};
+            wide_sparse(method, h->max_deg, out);
+        }
         return true;
     }
     const char *wide = getenv("LASSIM_SPARSE_WIDE");      // A/B: the coarser steps 128 / 512 only
@@ -388,7 +424,13 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
 int series_mode(const lassim_handle *h, const KernelChoice &kc, int N, bool periph) {
     if (periph) return 0;
     const bool automatic = h->speculate == 2;
+    // (beyond 16 genes the hand-over is on request only: a batch of 50-gene candidates is bound by
+    // the total work of its knock-down trajectories, not by its longest time series - config 3:
+    // 71 ms without, 97-107 ms with the hand-over, whose CTAs then share every SM with the
+    // knock-down kernel; alone, the longest time series takes 35 ms instead of 46)
     if (kc.fn_pirk3 != nullptr && (h->speculate == 5 || (automatic && N <= 16384))) return 5;
+    if (kc.fn_wide != nullptr && h->speculate == 5) return 5;
+    if (kc.fn_wide != nullptr && (h->speculate == 3 || h->speculate == 4 || h->speculate == 6)) return 3;
     if (kc.fn_pirk3 != nullptr && h->speculate == 6) return 6;
     if (kc.fn_pirk2 != nullptr && h->speculate == 4) return 4;
     if (kc.fn_pirk != nullptr && h->speculate == 3) return 3;
@@ -422,7 +464,9 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
                    cudaStream_t s, unsigned int *counters, const Scratch &sc, bool time_it) {
     // time-series kernel of the batch (series_mode above)
     const int smode = series_mode(h, kc, N, periph);
-    const kernel_fn series_fn = smode == 6 ? kc.fn_pirk3 : smode >= 4 ? kc.fn_pirk2 : smode == 3 ? kc.fn_pirk
+    const bool wide = kc.fn_wide != nullptr;
+    const kernel_fn series_fn = wide ? (smode >= 3 ? kc.fn_wide : nullptr)
+                              : smode == 6 ? kc.fn_pirk3 : smode >= 4 ? kc.fn_pirk2 : smode == 3 ? kc.fn_pirk
                               : smode == 1 ? kc.fn_shadow : nullptr;
     const bool speculate = series_fn != nullptr;
     auto launch = [&](kernel_fn fn, int threads, size_t smem, int lanes_per_item, unsigned begin,
@@ -473,7 +517,10 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
             // the cap of attempts continue in the multi-warp stage-parallel kernel behind it
             CU(launch(kc.fn_capped, threads, smem, kc.L, 0u, (unsigned)N, counters, s, series_cap_for(h, N), 0));
             if (time_it) CU(cudaEventRecord(h->ev_sp0, s));
-            if (handover_warps_for(h, N) == 3)
+            if (wide)
+                CU(launch(kc.fn_wide, kc.wide_threads, kc.wide_smem, kc.wide_threads, 0u, (unsigned)N,
+                          counters + 3, s, 0u, 1));
+            else if (handover_warps_for(h, N) == 3)
                 CU(launch(kc.fn_pirk3, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters + 3,
                           s, 0u, 1));
             else
@@ -483,7 +530,9 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
             CU(launch(series_fn, threads, smem, 32, 0u, (unsigned)N, counters, s));
         } else {
             if (time_it) CU(cudaEventRecord(h->ev_sp0, s));
-            if (smode == 6)
+            if (wide)
+                CU(launch(series_fn, kc.wide_threads, kc.wide_smem, kc.wide_threads, 0u, (unsigned)N, counters, s));
+            else if (smode == 6)
                 CU(launch(series_fn, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters, s));
             else if (smode == 4)
                 CU(launch(series_fn, pirk_threads(2), kc.pirk2_smem, 64, 0u, (unsigned)N, counters, s));
@@ -855,10 +904,11 @@ long long lassim_series_flops_per_attempt(const lassim_handle *h, int N) {
             // S stages, M = S corrections: (M+1)*S RHS evaluations of 2*nnz + 5*n flops,
             // M*S stage sums and the predictor (2*S flops per gene each), two weighted
             // sums for solution and estimate (2*S each), 4 for the error measure
-            const long long S = h->n <= 12 ? 5 : 4, M = S;
+            const long long S = (h->n <= 12 || h->n > 16) ? 5 : 4, M = S;
             const long long one = (M + 1) * S * (2 * nnz + 5 * n) + (M * S + S + 2) * 2 * S * n + 4 * n;
-            // every warp of a trajectory's group works
-            const long long warps = smode == 6 ? 3 : smode == 5 ? handover_warps_for(h, N) : smode == 4 ? 2 : 1;
+            // every warp of a trajectory's group works (one step size beyond 16 genes)
+            const long long warps = kc.fn_wide != nullptr ? 1
+                                  : smode == 6 ? 3 : smode == 5 ? handover_warps_for(h, N) : smode == 4 ? 2 : 1;
             return warps * one;
         }
         case 1: return 2 * lassim_flops_per_attempt(h);     // both halves of the warp
@@ -886,6 +936,12 @@ const char *lassim_series_kernel_name(lassim_handle *h, int N) {
         case 4:
         case 5:
         case 6: {
+            if (kc.fn_wide != nullptr) {
+                h->series_kernel_name = std::string(h->n <= 32 ? "grn_series_pirk_wide_kernel<5 Gauss stages x 32 lanes>"
+                                                               : "grn_series_pirk_wide_kernel<5 Gauss stages x 64 lanes>") +
+                                        (smode == 5 ? " behind " + std::string(lassim_kernel_name(h)) : "");
+                break;
+            }
             const int warps = smode == 6 ? 3 : smode == 5 ? handover_warps_for(h, N) : smode == 4 ? 2 : 1;
             h->series_kernel_name = std::string(h->n <= 12 ? "grn_series_pirk_kernel<5 Gauss stages x 6 lanes"
                                                             : "grn_series_pirk_kernel<4 Gauss stages x 8 lanes") +

@@ -466,6 +466,46 @@ def test_stage_parallel_kernels_on_small_problems(engine, n, pert):
     engine.set_speculation("auto")
 
 
+@pytest.mark.parametrize("n,pert,density", [
+    (17, True, 0.5), (24, False, 0.4),        # 5 stages x 32 lanes, dense rows (24 columns)
+    (32, True, 0.3),                          # dense rows, 32 columns
+    (33, True, 0.1), (50, False, 0.1),        # 5 stages x 64 lanes, ELL rows
+    (40, False, 0.5), (64, True, 0.3),        # in-degree > 8: CSR rows
+])
+def test_wide_stage_parallel_kernel(engine, n, pert, density):
+    """The CTA-per-trajectory Gauss kernel for 17 .. 64 genes (csrc/pirk_wide_kernel.cuh): all
+    time series in it ('stages'), and behind a hand-over after 5 attempts, against the oracle
+    at tight tolerance - the gates of the standard kernel."""
+    p, X = random_problem(n, 5, seed=700 + n, density=density, pert=pert)
+    engine.set_tolerances()
+    engine.set_problem(p["data"], p["sigma"], p["times"], p["y0"], p["mask"], p["pert"], 0.7)
+    tight = orc.tight_ode()
+    want = [orc.core_cost(x, p["data"], p["sigma"], p["times"], p["y0"], p["vector_map"], p["mask"],
+                          tight, return_traj=True) for x in X]
+    engine.set_speculation("off")
+    base = engine.eval(X, details=True)
+    assert "wide" not in engine.series_kernel_name(len(X))
+    for mode in ("stages", "handover"):
+        engine.set_speculation(mode)
+        engine.set_series_cap(5 if mode == "handover" else 0)
+        assert "grn_series_pirk_wide_kernel" in engine.series_kernel_name(len(X))
+        out = engine.eval(X, details=True)
+        again = engine.eval(X, details=True)
+        np.testing.assert_array_equal(out["cost"], again["cost"])
+        assert engine.last_stage_parallel_attempts() > 0
+        np.testing.assert_array_equal(engine.last_traj_steps(len(X)).sum(axis=1),
+                                      out["counters"][:, :2].sum(axis=1))
+        Y = engine.trajectories(X)
+        assert (out["status"] == 0).all()
+        for c, (cm, Yt) in enumerate(want):
+            assert out["cost_main"][c] == pytest.approx(cm, rel=COST_RTOL)
+            np.testing.assert_allclose(Y[c], Yt, rtol=TRAJ_RTOL, atol=1e-7)
+        if pert:      # knock-down trajectories do not depend on the time-series kernel
+            np.testing.assert_array_equal(out["pert_cost"], base["pert_cost"])
+    engine.set_series_cap(0)
+    engine.set_speculation("auto")
+
+
 def test_synthetic_50_gene_golden(engine):
     """BASELINE config 3's problem (50 genes, in-degree 5): reference outputs in
     tests/golden/syn50.npz."""
