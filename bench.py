@@ -120,7 +120,8 @@ CONFIG_TEXT = {
     4: "synthetic 200-gene core (in-degree 5, nnz=1000, dim=1400, 202 ODE solves per "
        "candidate), population 8192, stiff regime lambda,vmax~U[10,20], default_rng(200)",
     5: "peripheral-gene sweep: 10,000 genes x 16 candidates against the fixed Th2 core "
-       "(one joint 13-state solve per candidate; no reference implementation exists)",
+       "(the core integrated once, every candidate a scalar equation driven by it; no reference "
+       "implementation exists)",
 }
 
 

@@ -185,10 +185,18 @@ int lassim_trajectories(lassim_handle *h, int N, const double *X, double *Y,
  * problem: gene p obeys
  *     dx_p/dt = -lambda_p x_p + vmax_p / (1 + exp(-sum_j w_pj x_j(t)))
  * where x_j(t) is the core trajectory produced by `core_x` (a decision vector
- * of the problem currently set, which must have no more than 31 genes); the
- * joint (n+1)-state system is integrated from (y0_core, y0_p) over the core's
- * sample times and the cost is the time-series cost (core_problem.py:89-90) of
- * the peripheral state alone:  sum_t (data_p[t] - x_p(t)/max_t x_p)^2 / sigma_p^2.
+ * of the problem currently set, which must have no more than 32 genes), from
+ * (y0_core, y0_p) over the core's sample times, and the cost is the time-series
+ * cost (core_problem.py:89-90) of the peripheral state alone:
+ *     sum_t (data_p[t] - x_p(t)/max_t x_p)^2 / sigma_p^2.
+ * The gene does not act back on the core, so lassim_set_peripheral integrates the
+ * core ONCE (8(5,3) pair with its 7th-order continuous extension, a hundred times
+ * tighter than the candidates' tolerances; an error here means core_x has no
+ * finite trajectory) and every candidate is a scalar equation driven by that
+ * trajectory: one thread per candidate, same tolerances, error weight and
+ * controller as everywhere.  lassim_set_peripheral_joint(h, 1) integrates the
+ * joint (n+1)-state system per candidate in the cost kernel instead (core of at
+ * most 31 genes; 13x the work for the Th2 core; kept as a cross-check).
  *   genes    number of peripheral genes
  *   data[genes*T], sigma[genes], y0[genes]
  *   mask[genes*n] non-zero where core gene j may regulate gene p (NULL = all)
@@ -199,6 +207,7 @@ int lassim_trajectories(lassim_handle *h, int N, const double *X, double *Y,
 int lassim_set_peripheral(lassim_handle *h, const double *core_x, int genes,
                           const double *data, const double *sigma, const double *y0,
                           const unsigned char *mask);
+int lassim_set_peripheral_joint(lassim_handle *h, int joint);
 int lassim_eval_peripheral(lassim_handle *h, int N, const int *gene, const double *Xp,
                            double *cost, int *status);
 /* Joint trajectories Y[N*T*(n+1)] of the same candidates (last column = x_p). */

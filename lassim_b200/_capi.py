@@ -82,6 +82,8 @@ def load_library():
                                            c_int_p]
     lib.lassim_peripheral_trajectories.argtypes = [H, ctypes.c_int, c_int_p, c_double_p,
                                                    c_double_p]
+    lib.lassim_set_peripheral_joint.argtypes = [H, ctypes.c_int]
+    lib.lassim_set_peripheral_joint.restype = ctypes.c_int
     for name in ("lassim_set_peripheral", "lassim_eval_peripheral",
                  "lassim_peripheral_trajectories"):
         getattr(lib, name).restype = ctypes.c_int
@@ -332,6 +334,12 @@ class Engine:
                                                     _dp(sigma), _dp(y0), mp),
                     "lassim_set_peripheral")
         self.p_genes = genes
+
+    def set_peripheral_joint(self, joint=True):
+        """True: integrate the joint (n+1)-state system per candidate (cross-check; call before
+        set_peripheral); False (default): the core once, one thread per candidate."""
+        self._check(self._lib.lassim_set_peripheral_joint(self._h, int(bool(joint))),
+                    "lassim_set_peripheral_joint")
 
     def _peripheral_args(self, gene, Xp):
         Xp = _f64(Xp)

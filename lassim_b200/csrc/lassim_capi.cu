@@ -6,6 +6,7 @@
 #include "grn_kernels.cuh"
 #include "pirk_kernel.cuh"
 #include "pirk_wide_kernel.cuh"
+#include "peripheral_kernels.cuh"
 #include "de_kernels.cuh"
 
 #include <cmath>
@@ -122,6 +123,17 @@ struct lassim_handle {
     DevBuf<double> d_core_x, d_pdata, d_psigma2, d_py0;
     DevBuf<unsigned char> d_pmask;
     DevBuf<int> d_pgene;
+    // ... the core integrated once (peripheral_kernels.cuh): its table of intervals with the
+    // interpolant's coefficients, valid for the tolerances it was built with
+    bool periph_joint = false;          // LASSIM_PERIPHERAL_JOINT=1: the joint (n+1)-state path
+    DevBuf<double> d_core_table, d_core_samples, d_pYs;
+    DevBuf<int> d_core_count, d_pstatus;
+    DevBuf<unsigned int> d_psteps;
+    DevBuf<unsigned long long> d_pcounters;
+    int core_intervals = -1;            // -1: not built
+    double core_rtol = 0.0, core_atol = 0.0;
+    float core_swing = 0.0f;
+    bool last_periph_march = false;
 
     // scratch of the evaluation entry points
     DevBuf<double> d_X, d_probe;
@@ -646,10 +658,116 @@ int launch_eval(lassim_handle *h, Scratch &sc, int N, int mode, const double *dX
     if (rc) return rc;
     if (is_main) {
         CU(cudaEventRecord(h->ev1, s));
+        h->last_periph_march = false;
         h->timed = true;
         h->last_N = N;
         h->last_had_E = (K > 1 && mode == 0);
     }
+    return LASSIM_OK;
+}
+
+// ---- peripheral genes: the core integrated once, one thread per candidate ------------------
+typedef void (*core_fn)(const DevProblem, const double *, const CoreTable, const double, const double);
+typedef void (*march_fn)(const PeriphBatch);
+
+template <int NC>
+void periph_kernels_nc(core_fn *core, march_fn *march) {
+    *core = core_dense_kernel<NC>;
+    *march = peripheral_march_kernel<NC>;
+}
+
+bool periph_kernels(int n, core_fn *core, march_fn *march, int *nc_out) {
+    const int nc = (n + 3) & ~3;
+    if (n > 32) return false;
+    if (nc <= 4) periph_kernels_nc<4>(core, march);
+    else if (nc <= 8) periph_kernels_nc<8>(core, march);
+    else if (nc <= 12) periph_kernels_nc<12>(core, march);
+    else if (nc <= 16) periph_kernels_nc<16>(core, march);
+    else if (nc <= 24) periph_kernels_nc<24>(core, march);
+    else periph_kernels_nc<32>(core, march);
+    *nc_out = nc <= 4 ? 4 : nc <= 8 ? 8 : nc <= 12 ? 12 : nc <= 16 ? 16 : nc <= 24 ? 24 : 32;
+    return true;
+}
+
+// The core is one trajectory: it is integrated a hundred times tighter than the candidates
+// (its error is then no part of theirs) and costs a few milliseconds per sweep.
+constexpr double kCoreTolFactor = 0.01;
+
+// Integrates the core of the peripheral set-up into h->d_core_table (blocks).  Re-run when
+// the tolerances change.
+int build_core_table(lassim_handle *h) {
+    core_fn core; march_fn march; int nc = 0;
+    if (!periph_kernels(h->n, &core, &march, &nc))
+        return fail(h, LASSIM_E_UNSUPPORTED,
+                    "peripheral genes need a core of at most 32 genes (core has %d)", h->n);
+    const int n = h->n, T = h->T;
+    DevProblem P{};
+    P.n = n; P.T = T; P.K = 1; P.U = 0; P.dim = h->dim; P.nnz = h->nnz;
+    P.times = h->d_times.p; P.y0 = h->d_y0.p; P.kidx = h->d_kidx.p;
+    P.max_steps = (unsigned int)(h->max_steps > 4000000000LL ? 4000000000LL : h->max_steps);
+    P.swing = h->jump_guard;
+    const size_t smem = ((size_t)kSmemHeader + nc + 2) * sizeof(double);
+    CU(h->d_core_count.reserve(1));
+    CU(h->d_core_samples.reserve((size_t)T * n));
+    int capacity = 1 << 14;
+    for (int attempt = 0; attempt < 4; ++attempt, capacity *= 8) {
+        CU(h->d_core_table.reserve((size_t)capacity * core_interval_doubles(n)));
+        CoreTable out{h->d_core_table.p, h->d_core_count.p, h->d_core_samples.p, capacity};
+        core<<<1, 32, smem, h->stream>>>(P, h->d_core_x.p, out, h->rtol * kCoreTolFactor,
+                                         h->atol * kCoreTolFactor);
+        CU(cudaGetLastError());
+        h->launches += 1;
+        int count = 0;
+        CU(cudaMemcpyAsync(&count, h->d_core_count.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        if (count >= 0) {
+            h->core_intervals = count;
+            h->core_rtol = h->rtol; h->core_atol = h->atol; h->core_swing = h->jump_guard;
+            return LASSIM_OK;
+        }
+        const int status = -1 - count;
+        if (status != 4)
+            return fail(h, LASSIM_E_INVALID,
+                        "the fixed core could not be integrated (%s): peripheral genes need a core "
+                        "solution with a finite trajectory",
+                        status == 1 ? "step budget used up" : "non-finite state or step-size underflow");
+    }
+    return fail(h, LASSIM_E_UNSUPPORTED, "the core trajectory needs more than %d steps", capacity / 8);
+}
+
+// Enqueues the march over the core's intervals for N candidates already on the device.
+int launch_periph_march(lassim_handle *h, int N, const double *dX, const int *d_gene, cudaStream_t s) {
+    if (h->core_intervals < 0 || h->core_rtol != h->rtol || h->core_atol != h->atol ||
+        h->core_swing != h->jump_guard) {
+        int rc = build_core_table(h);
+        if (rc) return rc;
+    }
+    core_fn core; march_fn march; int nc = 0;
+    periph_kernels(h->n, &core, &march, &nc);
+    CU(h->main.cost.reserve(N));
+    CU(h->d_pYs.reserve((size_t)h->T * N));
+    CU(h->d_pstatus.reserve(N));
+    CU(h->d_psteps.reserve(N));
+    CU(h->d_pcounters.reserve((size_t)3 * N));
+    PeriphBatch B{};
+    B.N = N; B.n = h->n; B.T = h->T; B.X = dX; B.pgene = d_gene;
+    B.pmask = h->d_pmask.p; B.pdata = h->d_pdata.p; B.psigma2 = h->d_psigma2.p; B.py0 = h->d_py0.p;
+    B.table = h->d_core_table.p; B.intervals = h->core_intervals;
+    B.Ys = h->d_pYs.p; B.cost = h->main.cost.p; B.status = h->d_pstatus.p; B.steps = h->d_psteps.p;
+    B.counters = h->d_pcounters.p;
+    B.rtol = h->rtol; B.atol = h->atol;
+    B.max_steps = (unsigned int)(h->max_steps > 4000000000LL ? 4000000000LL : h->max_steps);
+    B.swing = h->jump_guard;
+    CU(cudaEventRecord(h->ev0, s));
+    march<<<(N + 127) / 128, 128, 0, s>>>(B);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(h->ev1, s));
+    h->launches += 1;
+    h->timed = true;
+    h->sp_timed = false;
+    h->last_N = N;
+    h->last_had_E = false;
+    h->last_periph_march = true;
     return LASSIM_OK;
 }
 
@@ -713,6 +831,7 @@ int lassim_create(int device, lassim_handle **out) {
     if (const char *sp = getenv("LASSIM_HANDOVER_WARPS")) h->handover_warps = atoi(sp);
     if (const char *sp = getenv("LASSIM_DE_LANES")) h->de_lanes_wanted = atoi(sp);
     if (const char *sp = getenv("LASSIM_NO_IF")) h->no_if = atoi(sp);
+    if (const char *sp = getenv("LASSIM_PERIPHERAL_JOINT")) h->periph_joint = atoi(sp) != 0;
     if (const char *sp = getenv("LASSIM_JUMP_GUARD")) h->jump_guard = (float)atof(sp);
     double tab[kExpTable];
     for (int j = 0; j < kExpTable; ++j) tab[j] = exp2((double)j / (double)kExpTable);
@@ -733,6 +852,8 @@ int lassim_destroy(lassim_handle *h) {
     h->d_row_ptr.release(); h->d_col_idx.release();
     h->d_core_x.release(); h->d_pdata.release(); h->d_psigma2.release(); h->d_py0.release();
     h->d_pmask.release(); h->d_pgene.release();
+    h->d_core_table.release(); h->d_core_samples.release(); h->d_pYs.release();
+    h->d_core_count.release(); h->d_pstatus.release(); h->d_psteps.release(); h->d_pcounters.release();
     h->de_X.release(); h->de_F.release(); h->de_trial.release(); h->de_best.release();
     h->de_table.release(); h->de_lb.release(); h->de_ub.release();
     h->d_traj_prefix.release(); h->d_knock_ctrl.release();
@@ -771,6 +892,7 @@ int lassim_set_problem(lassim_handle *h, int n, int T, const double *times,
     CU(guard_.err);
     h->has_problem = false;
     h->p_genes = 0;
+    h->core_intervals = -1;
     h->de_ready = false;
     h->n = n; h->T = T; h->pert_factor = pert_factor;
     std::vector<double> sigma2(n);
@@ -835,6 +957,7 @@ int lassim_set_mask(lassim_handle *h, const unsigned char *mask) {
     // the peripheral set-up and the device populations were laid out for the old mask
     // (core_x is indexed through kidx, the populations have the old dimension)
     h->p_genes = 0;
+    h->core_intervals = -1;
     h->de_ready = false;
     return upload_mask(h, mask);
 }
@@ -1060,12 +1183,14 @@ int lassim_set_peripheral(lassim_handle *h, const double *core_x, int genes,
     if (!h->has_problem) return fail(h, LASSIM_E_STATE, "set_peripheral before set_problem");
     if (!core_x || genes < 1 || !data || !sigma || !y0)
         return fail(h, LASSIM_E_INVALID, "set_peripheral: genes=%d or a NULL array", genes);
-    if (h->n > 31)
+    if (h->n > 32 || (h->periph_joint && h->n > 31))
         return fail(h, LASSIM_E_UNSUPPORTED,
-                    "peripheral genes need a core of at most 31 genes (core has %d)", h->n);
+                    "peripheral genes need a core of at most %d genes (core has %d)",
+                    h->periph_joint ? 31 : 32, h->n);
     DeviceGuard guard_(h->device);
     CU(guard_.err);
     const int n = h->n, T = h->T;
+    h->core_intervals = -1;
     std::vector<double> sigma2(genes);
     for (int g = 0; g < genes; ++g) sigma2[g] = sigma[g] * sigma[g];
     std::vector<unsigned char> all;
@@ -1078,6 +1203,18 @@ int lassim_set_peripheral(lassim_handle *h, const double *core_x, int genes,
     if ((rc = upload(h, h->d_pmask, mask, (size_t)genes * n))) return rc;
     CU(cudaStreamSynchronize(h->stream));
     h->p_genes = genes;
+    // the core is integrated here, once for the sweep (a core that cannot be integrated is
+    // reported now, not by every evaluation)
+    if (!h->periph_joint && (rc = build_core_table(h))) { h->p_genes = 0; return rc; }
+    return LASSIM_OK;
+}
+
+int lassim_set_peripheral_joint(lassim_handle *h, int joint) {
+    if (!h) return LASSIM_E_INVALID;
+    if (joint && h->has_problem && h->n > 31)
+        return fail(h, LASSIM_E_UNSUPPORTED,
+                    "the joint peripheral path needs a core of at most 31 genes (core has %d)", h->n);
+    h->periph_joint = joint != 0;
     return LASSIM_OK;
 }
 
@@ -1101,8 +1238,19 @@ int lassim_eval_peripheral(lassim_handle *h, int N, const int *gene, const doubl
     CU(h->d_pgene.reserve((size_t)N));
     CU(cudaMemcpyAsync(h->d_X.p, Xp, sizeof(double) * (size_t)N * pdim, cudaMemcpyHostToDevice, s));
     CU(cudaMemcpyAsync(h->d_pgene.p, gene, sizeof(int) * (size_t)N, cudaMemcpyHostToDevice, s));
-    int rc = launch_eval(h, h->main, N, 0, h->d_X.p, nullptr, s, h->d_pgene.p);
-    if (rc) return rc;
+    int rc;
+    if (!h->periph_joint) {
+        // the core integrated once, one thread per candidate (peripheral_kernels.cuh)
+        if ((rc = launch_periph_march(h, N, h->d_X.p, h->d_pgene.p, s))) return rc;
+        CU(cudaMemcpyAsync(cost, h->main.cost.p, sizeof(double) * (size_t)N, cudaMemcpyDeviceToHost, s));
+        if (status) CU(cudaMemcpyAsync(status, h->d_pstatus.p, sizeof(int) * (size_t)N,
+                                       cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        return LASSIM_OK;
+    }
+    // the joint (n+1)-state system per candidate in the cost kernel (cross-check)
+    h->last_periph_march = false;
+    if ((rc = launch_eval(h, h->main, N, 0, h->d_X.p, nullptr, s, h->d_pgene.p))) return rc;
     const ZeroLayout z = zero_layout(N);
     CU(cudaMemcpyAsync(cost, h->main.cost.p, sizeof(double) * (size_t)N, cudaMemcpyDeviceToHost, s));
     if (status) CU(cudaMemcpyAsync(status, h->main.zero.p + z.off_status, sizeof(int) * (size_t)N,
@@ -1120,6 +1268,20 @@ int lassim_peripheral_trajectories(lassim_handle *h, int N, const int *gene, con
     if (rc || N == 0) return rc;
     DeviceGuard guard_(h->device);
     CU(guard_.err);
+    if (h->last_periph_march) {
+        // core columns from the one core solve, last column from the candidates' samples
+        const int n = h->n, T = h->T;
+        std::vector<double> core((size_t)T * n), ys((size_t)T * N);
+        CU(cudaMemcpy(core.data(), h->d_core_samples.p, sizeof(double) * core.size(), cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(ys.data(), h->d_pYs.p, sizeof(double) * ys.size(), cudaMemcpyDeviceToHost));
+        for (int c = 0; c < N; ++c)
+            for (int t = 0; t < T; ++t) {
+                double *row = Y + ((size_t)c * T + t) * (n + 1);
+                for (int j = 0; j < n; ++j) row[j] = core[(size_t)t * n + j];
+                row[n] = ys[(size_t)t * N + c];
+            }
+        return LASSIM_OK;
+    }
     CU(cudaMemcpy(Y, h->main.Y.p, sizeof(double) * (size_t)N * h->T * (h->n + 1),
                   cudaMemcpyDeviceToHost));
     return LASSIM_OK;

@@ -118,3 +118,73 @@ def test_a_new_mask_invalidates_the_peripheral_setup(th2):
     eng.set_peripheral(np.delete(core, 24), data, sigma, y0, mask)      # first k entry dropped
     assert np.isfinite(eng.eval_peripheral(gene, Xp)).all()
     eng.close()
+
+
+def test_core_integrated_once_agrees_with_the_joint_system(th2, th2_late):
+    """Two independent implementations of the same definition: the default path integrates
+    the core once (8(5,3) with its continuous extension) and marches every candidate as a
+    scalar equation through it, one thread each; set_peripheral_joint(True) integrates the
+    joint 13-state system per candidate in the cost kernel.  Uniform candidates in the full
+    parameter box against the best core of the late golden set (what BASELINE config 5 runs)."""
+    from lassim_b200 import Engine
+    core_x = th2_late["X"][int(np.argmin(th2_late["ref_cost_main"]))]
+    rng = np.random.default_rng(5)
+    genes, per = 40, 8
+    data = rng.uniform(0.05, 1.0, (genes, 6)); data /= data.max(axis=1, keepdims=True)
+    y0 = rng.uniform(0.05, 1.5, genes)
+    mask = rng.random((genes, 12)) < 0.7
+    lb = np.concatenate([[0, 0], np.full(12, -20.0)]); ub = np.full(14, 20.0)
+    Xp = rng.uniform(lb, ub, size=(genes * per, 14))
+    gene = np.repeat(np.arange(genes, dtype=np.int32), per)
+    out = {}
+    for joint in (False, True):
+        eng = Engine(0)
+        eng.set_problem(th2["data"], th2["sigma"], th2["times"], th2["y0"], th2["mask"], None, 0.0)
+        eng.set_peripheral_joint(joint)
+        eng.set_peripheral(core_x, data, 0.2, y0, mask)
+        cost, st = eng.eval_peripheral(gene, Xp, return_status=True)
+        again = eng.eval_peripheral(gene, Xp)
+        np.testing.assert_array_equal(cost, again)
+        assert (st == 0).all()
+        out[joint] = (cost, eng.peripheral_trajectories(gene[:16], Xp[:16]))
+        eng.close()
+    np.testing.assert_allclose(out[False][0], out[True][0], rtol=2e-6)
+    np.testing.assert_allclose(out[False][1], out[True][1], rtol=1e-5, atol=1e-7)
+    # and against the definition at tight tolerance, a few candidates
+    for i in (0, 9, 77, 200, 319):
+        want = orc.peripheral_cost(Xp[i], core_x, th2["times"], th2["y0"], th2["vector_map"],
+                                   th2["mask"], data[gene[i]], 0.2, y0[gene[i]], mask[gene[i]],
+                                   rtol=1e-13, atol=1e-13)
+        assert out[False][0][i] == pytest.approx(want, rel=1e-6)
+
+
+def test_peripheral_genes_against_a_32_gene_core():
+    """The core may have up to 32 genes (one warp integrates it); checked against the
+    definition, joint 33-state system through LSODA."""
+    from lassim_b200 import Engine
+    rng = np.random.default_rng(32)
+    n, T = 32, 5
+    maskc = rng.random((n, n)) < 0.2
+    maskc[np.arange(n), rng.integers(0, n, n)] = True
+    times = np.concatenate([[0.0], np.sort(rng.uniform(0.5, 8.0, T - 1))])
+    y0c = rng.uniform(0.2, 1.2, n)
+    nnz = int(maskc.sum())
+    core_x = np.concatenate([rng.uniform(0.05, 1.0, n), rng.uniform(0.2, 1.5, n),
+                             rng.uniform(-2, 2, nnz)])
+    eng = Engine(0)
+    eng.set_problem(np.zeros((T, n)), np.ones(n), times, y0c, maskc.reshape(-1), None, 0.0)
+    genes = 5
+    data = rng.uniform(0.1, 1.0, (genes, T))
+    sigma = rng.uniform(0.1, 0.4, genes)
+    y0 = rng.uniform(0.1, 1.2, genes)
+    Xp = np.concatenate([rng.uniform(0.05, 1.0, (genes, 1)), rng.uniform(0.2, 1.5, (genes, 1)),
+                         rng.uniform(-2, 2, (genes, n))], axis=1)
+    eng.set_peripheral(core_x, data, sigma, y0, None)
+    cost, st = eng.eval_peripheral(np.arange(genes, dtype=np.int32), Xp, return_status=True)
+    assert (st == 0).all()
+    vmap = np.where(maskc.reshape(-1), -1.0, 0.0)
+    for g in range(genes):
+        want = orc.peripheral_cost(Xp[g], core_x, times, y0c, vmap, maskc.reshape(-1), data[g],
+                                   sigma[g], y0[g], None, rtol=1e-13, atol=1e-13)
+        assert cost[g] == pytest.approx(want, rel=1e-6)
+    eng.close()
