@@ -19,7 +19,9 @@ N > 1   the island archipelago of the reference (source/core/base_optimization.p
         island (trial vectors -> cost evaluation -> selection, on the device), and after
         every `gen` = 2 steps (examples/optimization_de.json) the best individuals migrate
         round the ring: one NCCL all-reduce of [islands, dim + 1] doubles INSIDE the timed
-        region.  Ranks do not wait for each other between migrations.  `value` = candidates
+        region, posted without blocking and applied one round later (PyGMO's migration is
+        asynchronous too), so a rank waits for the others only when it is more than a round
+        ahead.  `value` = candidates
         all ranks evaluated / max-over-ranks device time.  `multi_gpu` carries the evidence
         that the exchange ran; `replicas` is the round-1 measurement (every rank the same
         population, no collective) kept as a labelled diagnostic.
@@ -738,21 +740,20 @@ def run_single(args, ctx):
     print(json.dumps(line), flush=True)
 
 
-def migrate(ctx, eng, n_islands):
+def migrate(ctx, eng, exchange):
     """PyGMO's default migration on a ring: every island sends its best, which replaces the
-    receiver's worst if better (one all-reduce of the table of bests; rows are disjoint)."""
-    torch = ctx.torch
-    mine = eng.de_best()                  # waits for this island's generations, then 704 B to the host
+    receiver's worst if better.  The table of bests is all-reduced without blocking and
+    applied one round later (lassim_b200/pygmo/migration.py): a rank waits for the others only
+    when it is more than a round ahead.  Returns (table applied or None, (ms to post, ms
+    waiting for the round before, ms to apply))."""
     t0 = time.perf_counter()
-    table = np.zeros((n_islands, mine.shape[1]))
-    table[ctx.rank::ctx.world] = mine
-    t = torch.from_numpy(table).cuda()
-    if ctx.world > 1:
-        ctx.dist.all_reduce(t)            # returns when every rank has contributed: includes the
-    table = t.cpu().numpy()               # wait for the slowest island of this round
+    mine = eng.de_best()                  # waits for this island's generations, then 704 B to the host
     t1 = time.perf_counter()
-    eng.de_migrate_ring(table, ctx.rank, ctx.world)
-    return table, ((t1 - t0) * 1e3, (time.perf_counter() - t1) * 1e3)
+    table = exchange.exchange({ctx.rank: mine[0]})
+    t2 = time.perf_counter()
+    if table is not None:
+        eng.de_migrate_ring(table, ctx.rank, ctx.world)
+    return table, ((t1 - t0) * 1e3, (t2 - t1) * 1e3, (time.perf_counter() - t2) * 1e3)
 
 
 def run_archipelago(args, ctx):
@@ -768,11 +769,13 @@ def run_archipelago(args, ctx):
     ext = torch.cuda.ExternalStream(eng.stream)
     fp64_peak = eng.fp64_peak_tflops(400000) if rank == 0 else None
 
+    from lassim_b200.pygmo.migration import RingExchange
+    exchange = RingExchange(ctx.dist if world > 1 else None, world, dim, delayed=not args.lockstep_migration)
     warm = max(args.warmup, 3)
     for k in range(warm):
         eng.de_evolve(1)
         if (k + 1) % DE_GEN == 0:
-            migrate(ctx, eng, world)
+            migrate(ctx, eng, exchange)
     torch.cuda.synchronize()
     sampler = ClockSampler(ctx.local)
     if rank == 0:
@@ -787,7 +790,8 @@ def run_archipelago(args, ctx):
     for k in range(args.steps):
         eng.de_evolve(1)                                     # enqueued; no host wait
         if (k + 1) % DE_GEN == 0:
-            table, ms = migrate(ctx, eng, world)
+            tb, ms = migrate(ctx, eng, exchange)
+            table = tb if tb is not None else table
             mig_ms.append(ms)
             migrations += 1
     e1.record(ext)
@@ -798,14 +802,17 @@ def run_archipelago(args, ctx):
     evals = eng.de_evaluations - evals0
     assert evals == POP * args.steps
     clocks = sampler.stop() if rank == 0 else None
-    ex_ms = float(np.mean([m[0] for m in mig_ms])) if mig_ms else 0.0
-    up_ms = float(np.mean([m[1] for m in mig_ms])) if mig_ms else 0.0
-    dev_ms_max, up_max = ctx.max_over_ranks([dev_ms, up_ms])
-    ex_min = -ctx.max_over_ranks([-ex_ms])[0]
+    own_ms = float(np.mean([m[0] for m in mig_ms])) if mig_ms else 0.0
+    wait_ms = float(np.mean([m[1] for m in mig_ms])) if mig_ms else 0.0
+    up_ms = float(np.mean([m[2] for m in mig_ms])) if mig_ms else 0.0
+    dev_ms_max, wait_max, up_max, own_max = ctx.max_over_ranks([dev_ms, wait_ms, up_ms, own_ms])
+    wait_min = -ctx.max_over_ranks([-wait_ms])[0]
     dev_ms_min = -ctx.max_over_ranks([-dev_ms])[0]
     # every rank holds the same table of bests after the all-reduce
+    last = exchange.flush()
+    table = last if last is not None else table
     if table is None:
-        table, _ = migrate(ctx, eng, world)
+        table = RingExchange(ctx.dist, world, dim, delayed=False).exchange({rank: eng.de_best()[0]})
     chk = float(np.nansum(table))
     agree = ctx.max_over_ranks([chk])[0] == -ctx.max_over_ranks([-chk])[0]
     Xf, Ff = eng.de_get()
@@ -884,11 +891,17 @@ def run_archipelago(args, ctx):
             "multi_gpu": {"islands": world, "individuals_per_island": POP,
                           "generations_per_round": DE_GEN, "migrations": migrations,
                           "migration_bytes": int(world * (dim + 1) * 8),
-                          "migration_ms": ex_min + up_max,
-                          "migration_note": "mean per migration of: the all-reduce with its host<->device "
-                                            "copies as seen by the rank that arrives last (%.3f ms; the other "
-                                            "ranks wait in it for that rank's island) + upload of the table "
-                                            "and the migration kernel (%.3f ms)" % (ex_min, up_max),
+                          "migration": ("lock-step: the table of round r is applied after round r"
+                                        if args.lockstep_migration else
+                                        "one round behind: the table of round r is all-reduced without "
+                                        "blocking and applied after round r + 1"),
+                          "migration_ms": wait_min + up_max,
+                          "migration_note": "mean per migration: posting the all-reduce and waiting for the "
+                                            "one before, least-waiting rank %.3f ms / most-waiting rank %.3f ms "
+                                            "(the difference is waiting for slower islands, not exchange) + "
+                                            "upload of the table and the migration kernel %.3f ms; reading the "
+                                            "island's best (waits for its own generations) %.3f ms"
+                                            % (wait_min, wait_max, up_max, own_max),
                           "collective": "torch.distributed all_reduce (NCCL) of the [islands, dim+1] "
                                         "table of bests",
                           "champions_agree_across_ranks": bool(agree),
@@ -1010,6 +1023,9 @@ def main():
                     help="BASELINE.json config (2 = the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-other-configs", action="store_true")
+    ap.add_argument("--lockstep-migration", action="store_true",
+                    help="N > 1: apply every round's table of bests in that round (ranks then wait "
+                         "for the slowest island of every round)")
     ap.add_argument("--c4-population", type=int, default=0,
                     help="config 4 with fewer than its 8192 candidates (0 = all)")
     ap.add_argument("--method", default=os.environ.get("LASSIM_METHOD", "dop853"),

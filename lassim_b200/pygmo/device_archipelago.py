@@ -4,9 +4,13 @@ Same interface and migration policy as `archipelago` (archipelago.py), but the
 populations of this rank's islands stay in device memory and a whole evolve
 round - `gen` generations of trial vectors, evaluation and selection - is
 enqueued without a host round trip (lassim_de_* in include/lassim_b200.h).  The
-host only sees the islands' best individuals once per round (ring migration,
-exchanged across ranks when torch.distributed is initialised) and the final
-populations at `join()`.
+host only sees the islands' best individuals once per round (ring migration;
+across ranks - torch.distributed initialised - the table of bests is all-reduced
+without blocking and applied one round later, pygmo/migration.py) and the final
+populations at `join()`.  Inside a round the islands of a GPU do not wait for
+each other either (lassim_de_set_lanes).  The early-stop test on xtol/ftol stops
+a round only when ALL islands of the GPU have collapsed (the host driver stops
+each island on its own).
 
 Needs a problem evaluated by lassim_b200's GPU plugins (CoreProblem /
 CoreWithPerturbationsProblem) and the DE algorithm; the early-stop test on
@@ -15,11 +19,12 @@ import numpy as np
 
 from . import topology as _topology
 from .archipelago import _dist, island
+from .migration import RingExchange
 
 
 class device_archipelago:
     def __init__(self, algo=None, prob=None, n_islands=0, n_individuals=0, topology=None,
-                 seed=None):
+                 seed=None, delayed_migration=True):
         self.topology = topology if topology is not None else _topology.unconnected()
         if not isinstance(self.topology, (_topology.unconnected, _topology.ring)):
             raise NotImplementedError("device archipelago: unconnected or ring topology")
@@ -28,6 +33,10 @@ class device_archipelago:
         self._seed = int(self._seed_seq.generate_state(1, dtype=np.uint64)[0])
         self._engine = None
         self._stale = True
+        self._exchange = None
+        # across ranks the bests travel one round behind, so that no rank waits for the slowest
+        # island of every round (pygmo/migration.py); irrelevant in a single process
+        self._delayed = bool(delayed_migration)
         self.evaluations = 0
         for _ in range(int(n_islands)):
             self.push_back(island(algo, prob, n_individuals, seed=self._seed_seq.spawn(1)[0]))
@@ -111,22 +120,32 @@ class device_archipelago:
             table = t.cpu().numpy()
         return table
 
-    def _migrate(self):
-        if len(self._islands) < 2 or isinstance(self.topology, _topology.unconnected):
-            return
-        table = self._table()
-        if not self._own:
+    def _apply(self, table):
+        if table is None or not self._own:
             return
         # islands are dealt round-robin to ranks: local island j is ring member
         # own[0] + j * world
         stride = self._own[1] - self._own[0] if len(self._own) > 1 else 1
         self._engine.de_migrate_ring(table, self._own[0], stride)
 
+    def _migrate(self):
+        if len(self._islands) < 2 or isinstance(self.topology, _topology.unconnected):
+            return
+        if self._exchange is None:
+            dim = self._islands[0].population.X.shape[1]
+            self._exchange = RingExchange(_dist(), len(self._islands), dim, self._delayed)
+        rows = {}
+        if self._own:
+            rows = dict(zip(self._own, self._engine.de_best()))
+        self._apply(self._exchange.exchange(rows))
+
     def join(self):
         """Bring the populations (owned islands) and every island's champion
         (all ranks) back to the host-side island objects."""
         if self._engine is None:
             self._start()
+        if self._exchange is not None:
+            self._apply(self._exchange.flush())          # the bests of the last round
         table = self._table()
         if self._own:
             X, F = self._engine.de_get()

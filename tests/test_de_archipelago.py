@@ -188,3 +188,52 @@ def test_exponential_crossover_length_is_pagmos():
     changed = trial != X
     starts = (changed & ~np.roll(changed, 1, axis=1)).sum(axis=1)
     assert ((starts == 1) | (length == D)).all()
+
+
+EXCHANGE_SCRIPT = r"""
+import os, sys, time
+import numpy as np
+import torch.distributed as dist
+sys.path.insert(0, {repo!r})
+from lassim_b200.pygmo.migration import RingExchange
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+n_isl, dim = 4, 3
+got = {{}}
+for delayed in (True, False):
+    ex = RingExchange(dist, n_isl, dim, delayed=delayed)
+    tables = []
+    for r in range(3):
+        if rank == 1:
+            time.sleep(0.05)            # a slower island: nobody may see a half-filled table
+        rows = {{i: np.full(dim + 1, 100.0 * r + i) for i in range(rank, n_isl, world)}}
+        tables.append(ex.exchange(rows))
+    tables.append(ex.flush())
+    got[delayed] = tables
+want = [np.tile((100.0 * r + np.arange(n_isl))[:, None], (1, dim + 1)) for r in range(3)]
+# one round behind: nothing after round 0, then rounds 0, 1 and - from flush - round 2
+assert got[True][0] is None
+for r in range(3):
+    np.testing.assert_array_equal(got[True][r + 1], want[r])
+    np.testing.assert_array_equal(got[False][r], want[r])
+assert got[False][3] is None
+dist.destroy_process_group()
+"""
+
+
+def test_ring_exchange_between_two_ranks(tmp_path):
+    """The table of bests crosses ranks complete, in lock-step or one round behind."""
+    script = tmp_path / "run.py"
+    script.write_text(EXCHANGE_SCRIPT.format(repo=REPO))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29537", str(script)]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+
+
+def test_ring_exchange_in_one_process():
+    from lassim_b200.pygmo.migration import RingExchange
+    ex = RingExchange(None, 3, 2)
+    t = ex.exchange({0: np.array([1.0, 2.0, 3.0]), 2: np.array([4.0, 5.0, 6.0])})
+    np.testing.assert_array_equal(t, [[1, 2, 3], [0, 0, 0], [4, 5, 6]])
+    assert ex.flush() is None
