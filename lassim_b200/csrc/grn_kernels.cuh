@@ -108,8 +108,13 @@ constexpr int threads_for(int L) { return L > 32 ? L : (L == 4 ? 256 : 128); }
 #ifndef LASSIM_MIN_BLOCKS_32
 #define LASSIM_MIN_BLOCKS_32 2
 #endif
+// CTA-wide groups (L > 32): the register budget is 65536 / (L * blocks)
+#ifndef LASSIM_MIN_BLOCKS_WIDE
+#define LASSIM_MIN_BLOCKS_WIDE 1
+#endif
 constexpr int min_blocks_for(int L) {
-    return L == 16 ? LASSIM_MIN_BLOCKS : L == 32 ? LASSIM_MIN_BLOCKS_32 : 1;
+    return L == 16 ? LASSIM_MIN_BLOCKS : L == 32 ? LASSIM_MIN_BLOCKS_32
+         : (L * LASSIM_MIN_BLOCKS_WIDE <= 1024 ? LASSIM_MIN_BLOCKS_WIDE : 1);
 }
 
 // doubles of shared memory in front of the groups' exchange lines: the 2^(j/256) table
