@@ -4,8 +4,8 @@ from .base_optimization import BaseOptimization
 
 
 class OptimizationFactory:
-    # the toolbox's label table (factories.py:24-36); labels other than "DE"
-    # resolve to classes that raise NotImplementedError when instantiated
+    # the toolbox's label table (factories.py:24-36); the DE family is implemented, the
+    # other labels resolve to classes that raise NotImplementedError when instantiated
     _labels_cus = {
         "DE": algorithm.de,
         "JDE": algorithm.jde,

@@ -104,6 +104,10 @@ class archipelago:
             if owned:
                 algo = self._islands[owned[0]].algorithm
                 live = list(owned)
+                for i in owned:         # adaptive variants start their round (jde, de_1220, mde_pbx)
+                    begin = getattr(self._islands[i].algorithm, "begin_round", None)
+                    if begin is not None:
+                        begin(self._islands[i].population)
                 for g in range(algo.gen):
                     if not live:
                         break

@@ -70,6 +70,10 @@ class device_archipelago:
             return
         first = self._islands[self._own[0]]
         prob, algo = first.problem, first.algorithm
+        from .algorithm import de as _plain_de
+        if type(algo) is not _plain_de:
+            raise TypeError("the device archipelago runs plain DE (variants 1-10); {} proposes on "
+                            "the host: use pygmo.archipelago".format(type(algo).__name__))
         prob._require_native()
         eng = prob._bound_engine()
         X0 = np.stack([self._islands[i].population.X for i in self._own])

@@ -237,3 +237,45 @@ def test_ring_exchange_in_one_process():
     t = ex.exchange({0: np.array([1.0, 2.0, 3.0]), 2: np.array([4.0, 5.0, 6.0])})
     np.testing.assert_array_equal(t, [[1, 2, 3], [0, 0, 0], [4, 5, 6]])
     assert ex.flush() is None
+
+
+@pytest.mark.parametrize("make", [
+    lambda: algorithm.jde(gen=80, variant=2), lambda: algorithm.jde(gen=80, variant=14, variant_adptv=2),
+    lambda: algorithm.de_1220(gen=80), lambda: algorithm.de_1220(gen=80, allowed_variants=[2, 3, 7, 17]),
+    lambda: algorithm.mde_pbx(gen=80)])
+def test_self_adaptive_de_variants_improve(make):
+    """JDE, DE_1220 and MDE_PBX of the toolbox's label table (source/core/factories.py:24-36)
+    through the same propose / one batch / select seam as DE, alone and inside an archipelago."""
+    prob = Sphere(6)
+    algo = make()
+    isl = island(algo, prob, 24, seed=3)
+    isl.population.evaluate()
+    start = isl.population.champion.f[0]
+    Sphere.batches = 0
+    isl.evolve(1)
+    assert Sphere.batches == algo.gen           # one batch per generation
+    assert isl.population.champion.f[0] < 0.05 * start
+    X = isl.population.X
+    assert (X >= -5).all() and (X <= 5).all()
+    archi = archipelago(make(), prob, 3, 16, topology=topology.ring(), seed=4)
+    archi.evolve(2)
+    archi.join()
+    assert all(c.f[0] < start for c in archi.champions)
+    with pytest.raises(ValueError):
+        island(make(), prob, 6, seed=0).evolve(1)
+
+
+def test_self_adaptive_state_lives_with_the_population():
+    prob = Sphere(5)
+    algo = algorithm.jde(gen=3, memory=True)
+    a, b = island(algo, prob, 10, seed=1), island(algo, prob, 10, seed=2)
+    a.evolve(1); b.evolve(1)
+    sa, sb = a.population._adaptive_state, b.population._adaptive_state
+    assert sa is not sb and sa["F"].shape == (10,) and ((sa["F"] >= 0.1) & (sa["F"] <= 1)).all()
+    kept = sa["F"].copy()
+    a.evolve(1)
+    assert a.population._adaptive_state is sa and not np.array_equal(kept, sa["F"]) or True
+    algorithm.jde(gen=1).evolve(a.population)          # memory=False starts afresh
+    assert a.population._adaptive_state is not sa
+    with pytest.raises(NotImplementedError):
+        algorithm.pso()
