@@ -533,10 +533,13 @@ def roofline_dict(eng, N, peak, k_ms, d_ms, series_attempts, attempts):
     achieved = series_attempts * series_flops / (d_ms * 1e-3) / 1e12
     return {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
             "frac": achieved / peak if peak else None,
-            "traffic": None,
-            "traffic_note": "the path is compute-bound (X in + cost out = 0.72 MB per step); the "
-                            "dram bytes of the three kernels are in profiles/ (ncu --set full), "
-                            "not re-measured in this run",
+            # dram__bytes_read.sum + dram__bytes_write.sum of this kernel, per launch
+            "traffic": 512512,
+            "traffic_source": "STATIC: one ncu --set full capture of this kernel on the same "
+                              "workload (profiles/r2_d_ncu_full_summary.txt), not re-measured in "
+                              "this run; the evaluation's three kernels together read 2.28 MB and "
+                              "write nothing back to DRAM, against 0.72 MB of X in + cost out: the "
+                              "path is compute-bound",
             "kernel": eng.series_kernel_name(N), "kernel_ms": d_ms,
             "attempts_per_launch": series_attempts, "flops_per_attempt": series_flops,
             "share_of_step": d_ms / k_ms,
