@@ -978,8 +978,17 @@ def other_config(args, ctx, config, peak, with_cpu=True):
         ms = eng.last_kernel_ms()
         ctx.barrier()
         wall_max, ms_max = ctx.max_over_ranks([wall, ms])
-        bad = ctx.sum_over_ranks([float((st != 0).sum())])[0]
+        att = float(eng.last_traj_steps(len(gene_l))[:, 0].sum())
+        # algorithmic flops of one attempt of the scalar equation: 12 right-hand sides of
+        # 2 n + 5 (the regulator sum over the n core genes, SURVEY 8d's F_rhs for one gene with
+        # in-degree n) + the 8(5,3) tableau for one state (212)
+        flops_att = 12 * (2 * 12 + 5) + 212
+        bad, att_all = ctx.sum_over_ranks([float((st != 0).sum()), att])
+        tf = att_all * flops_att / (ms_max * 1e-3) / 1e12
         res.update(candidates=len(gene), candidates_per_gpu=len(gene_l), genes=int(gene.max()) + 1,
+                   kernel="peripheral_march_kernel (core integrated once, one thread per candidate)",
+                   step_attempts=att_all, flops_per_attempt=flops_att, achieved_tflops=tf,
+                   roofline_frac=tf / (peak * world) if peak else None,
                    kernel_ms=ms_max, evals_per_s=len(gene) / (ms_max * 1e-3),
                    e2e_evals_per_s=len(gene) / wall_max, status_not_ok=int(bad),
                    parity="unpinned: the reference has no peripheral-gene code (README.md:77-80); "

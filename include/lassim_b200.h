@@ -273,7 +273,8 @@ long long lassim_de_evaluations(const lassim_handle *h);
 int lassim_last_end_states(lassim_handle *h, int N, double *E);
 
 /* Step attempts per trajectory of the LAST evaluation: steps[N*K] (after
- * lassim_trajectories only slot 0 of each candidate is non-zero). */
+ * lassim_trajectories or lassim_eval_peripheral only slot 0 of each candidate is
+ * non-zero). */
 int lassim_last_traj_steps(lassim_handle *h, int N, unsigned int *steps);
 
 /*

@@ -1305,6 +1305,14 @@ int lassim_last_traj_steps(lassim_handle *h, int N, unsigned int *steps) {
     DeviceGuard guard_(h->device);
     CU(guard_.err);
     CU(cudaDeviceSynchronize());
+    if (h->last_periph_march) {
+        // one solve per candidate: its attempts in slot 0, the other K - 1 slots zero
+        std::vector<unsigned> one((size_t)N);
+        CU(cudaMemcpy(one.data(), h->d_psteps.p, sizeof(unsigned) * (size_t)N, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < (size_t)N * h->K; ++i) steps[i] = 0u;
+        for (int i = 0; i < N; ++i) steps[(size_t)i * h->K] = one[i];
+        return LASSIM_OK;
+    }
     CU(cudaMemcpy(steps, h->main.steps.p, sizeof(unsigned) * (size_t)N * h->K, cudaMemcpyDeviceToHost));
     return LASSIM_OK;
 }

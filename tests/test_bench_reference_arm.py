@@ -28,3 +28,26 @@ def test_other_ranks_of_the_reference_arm_do_nothing():
                           "--steps", "1", "--warmup", "0"], capture_output=True, text=True,
                          timeout=300, env=env)
     assert res.returncode == 0 and res.stdout.strip() == ""
+
+
+def test_parity_block_of_the_bench_line():
+    """bench.py's `parity` block on synthetic 'device results': the reference's own outputs pass
+    every gate; a time-series cost off by 1e-5 on a converged row does not."""
+    import sys
+    import numpy as np
+    sys.path.insert(0, REPO)
+    import bench
+    g = dict(np.load(os.path.join(REPO, "tests", "golden", "th2_uniform_full.npz")))
+    E = np.concatenate([np.zeros((1024, 1, 12)), g["tight_ctrl_end"], g["tight_knock_end"]], axis=1)
+    out = {"cost": g["ref_total"].copy(), "cost_main": g["ref_cost_main"].copy(),
+           "pert_cost": g["ref_pert_cost"].copy(), "status": np.zeros(1024, dtype=np.int32), "E": E}
+    block = bench.parity_block(out)
+    assert block["ok"] and block["rows"] == 1024
+    assert block["converged_rows"]["cost_main"] == 997
+    assert block["knock_down_end_states"]["rows_within_1e-5_of_converged"] == 1024
+    assert block["nan_rows_gpu"] == [] and block["nan_rows_agree"]
+    out["cost_main"][0] *= 1 + 1e-5
+    assert not bench.parity_block(out)["ok"]
+    out["cost_main"][0] = g["ref_cost_main"][0]
+    out["status"][5] = 1
+    assert not bench.parity_block(out)["ok"]

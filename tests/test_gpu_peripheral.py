@@ -146,6 +146,8 @@ def test_core_integrated_once_agrees_with_the_joint_system(th2, th2_late):
         again = eng.eval_peripheral(gene, Xp)
         np.testing.assert_array_equal(cost, again)
         assert (st == 0).all()
+        steps = eng.last_traj_steps(len(gene))
+        assert (steps[:, 0] > 0).all() and (steps[:, 1:] == 0).all()
         out[joint] = (cost, eng.peripheral_trajectories(gene[:16], Xp[:16]))
         eng.close()
     np.testing.assert_allclose(out[False][0], out[True][0], rtol=2e-6)
