@@ -479,6 +479,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
     // integrating factor for growing genes (rk_steppers.cuh): standard kernels only
     constexpr bool kIF = !SHADOW && !PERIPH;
     double y[R], k1[R], yn[R], kn[R], lam[R], vm[R], gr[R];
+    int sprev[R], snext[R];            // logistic values (high words) at y / at yn: jump guard
     WT wts;
     wts.clear();                       // finite placeholders until work arrives
     bool gene_ok[R];
@@ -486,6 +487,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
     for (int r = 0; r < R; ++r) {
         gene_ok[r] = (lg * R + r) < n;
         y[r] = 0.0; k1[r] = 0.0; lam[r] = 0.0; vm[r] = 0.0; gr[r] = 0.0;
+        sprev[r] = 0x3fe00000; snext[r] = 0x3fe00000;      // 0.5: what a parked lane computes
     }
 
     bool active = false, exhausted = false;
@@ -596,6 +598,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
                     sg[r] = fma(sg[r], se[r], sg[r]);
+                    sprev[r] = __double2hiint(sg[r]);
                     k1[r] = fma(vm[r], sg[r], -lam[r] * y[r]);
                 }
                 // (k1 is the derivative without the growth term; the norms use all of it)
@@ -659,17 +662,17 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
             if constexpr (METHOD == kMethodDOP853) {
                 if (use_if)
                     qf = dop853_attempt<kIF, R>(sig_step, gmax_step, lam, vm, gr, tab, y, k1, hs,
-                                                rtol, atol, P.swing, yn, kn);
+                                                rtol, atol, P.swing, sprev, snext, yn, kn);
                 else
                     qf = dop853_attempt<false, R>(sig_step, gmax_step, lam, vm, gr, tab, y, k1, hs,
-                                                  rtol, atol, P.swing, yn, kn);
+                                                  rtol, atol, P.swing, sprev, snext, yn, kn);
             } else {
                 if (use_if)
                     qf = dp45_attempt<kIF, R>(sig_step, gmax_step, lam, vm, gr, tab, y, k1, hs,
-                                              rtol, atol, P.swing, yn, kn);
+                                              rtol, atol, P.swing, sprev, snext, yn, kn);
                 else
                     qf = dp45_attempt<false, R>(sig_step, gmax_step, lam, vm, gr, tab, y, k1, hs,
-                                                rtol, atol, P.swing, yn, kn);
+                                                rtol, atol, P.swing, sprev, snext, yn, kn);
             }
 
             bool fallback = false;     // the shorter attempt is the one that counts
@@ -684,7 +687,8 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                 for (int r = 0; r < R; ++r) {
                     const double yo = __shfl_xor_sync(0xffffffffu, yn[r], 16);
                     const double ko = __shfl_xor_sync(0xffffffffu, kn[r], 16);
-                    if (!mine) { yn[r] = yo; kn[r] = ko; }
+                    const int so = __shfl_xor_sync(0xffffffffu, snext[r], 16);
+                    if (!mine) { yn[r] = yo; kn[r] = ko; snext[r] = so; }
                 }
                 qf = fallback ? q_short : q_full;
                 hs = fallback ? hs_full * kShadowRatio : hs_full;
@@ -700,7 +704,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                     ++nacc;
                     t = hit ? tend : t + hs;
 #pragma unroll
-                    for (int r = 0; r < R; ++r) { y[r] = yn[r]; k1[r] = kn[r]; }
+                    for (int r = 0; r < R; ++r) { y[r] = yn[r]; k1[r] = kn[r]; sprev[r] = snext[r]; }
                     float fac = fminf(LASSIM_FACMAX, fmaxf(0.2f, fac0));
                     if (rejected) fac = fminf(fac, 1.0f);
                     rejected = fallback;     // the proposed step did fail: no growth next time
@@ -809,7 +813,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
             // park: until new work arrives this group only goes through the
             // motions of the step loop with its warp; keep its registers finite
 #pragma unroll
-            for (int r = 0; r < R; ++r) { y[r] = 0.0; k1[r] = 0.0; gr[r] = 0.0; }
+            for (int r = 0; r < R; ++r) { y[r] = 0.0; k1[r] = 0.0; gr[r] = 0.0; sprev[r] = 0x3fe00000; }
             grow = false;
             h = 0.0; t = 0.0; tend = 0.0;
             if (B.mode == 0 && !handover) {

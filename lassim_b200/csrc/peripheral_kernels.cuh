@@ -68,6 +68,7 @@ core_dense_kernel(const DevProblem P, const double *__restrict__ core_x, const C
     double lam = 0.0, vm = 0.0, y = 0.0;
     if (ok) { lam = core_x[g]; vm = core_x[n + g]; y = P.y0[g]; }
     int slo = 0x7ff00000, shi = 0;                 // logistic swing over an attempt (jump guard)
+    int slast = 0x3fe00000;                        // logistic value of the last evaluation
     auto rhs = [&](double yin) {
         if (g < NC) ybuf[g] = yin;
         __syncwarp();
@@ -77,7 +78,8 @@ core_dense_kernel(const DevProblem P, const double *__restrict__ core_x, const C
         double sr, se;
         logistic_fast_parts(z[0], tab, sr, se);
         const double sg = fma(sr, se, sr);
-        slo = min(slo, __double2hiint(sg)); shi = max(shi, __double2hiint(sg));
+        slast = __double2hiint(sg);
+        slo = min(slo, slast); shi = max(shi, slast);
         return fma(vm, sg, -lam * yin);
     };
     auto wmax = [&](double v) {
@@ -91,6 +93,7 @@ core_dense_kernel(const DevProblem P, const double *__restrict__ core_x, const C
     if (ok) out.samples[g] = y;
     double K[D::kExtended];
     K[0] = rhs(y);
+    int sprev = slast;                             // logistic value at y: where an attempt's swing starts
     // starting step (Hairer/Norsett/Wanner II.4, max-norm), as in the cost kernels
     double h;
     {
@@ -112,7 +115,7 @@ core_dense_kernel(const DevProblem P, const double *__restrict__ core_x, const C
             double hs = h;
             bool hit = false;
             if (t + 1.01 * hs >= tend) { hs = tend - t; hit = true; }
-            slo = 0x7ff00000; shi = 0;
+            slo = sprev; shi = sprev;
 #pragma unroll
             for (int s = 1; s < D::kStages; ++s) {
                 double acc = 0.0;
@@ -130,6 +133,7 @@ core_dense_kernel(const DevProblem P, const double *__restrict__ core_x, const C
                 yn = fma(hs, acc, y);
             }
             K[D::kStages] = rhs(yn);
+            const int snew = slast;
             double e5 = 0.0, e3 = 0.0;
 #pragma unroll
             for (int j = 0; j <= D::kStages; ++j) {
@@ -181,6 +185,7 @@ core_dense_kernel(const DevProblem P, const double *__restrict__ core_x, const C
                 ++k;
                 t = hit ? tend : t + hs;
                 y = yn;
+                sprev = snew;
                 K[0] = K[D::kStages];
                 double fac = fmin(10.0, fmax(0.2, fac0));
                 if (rejected) fac = fmin(fac, 1.0);
@@ -251,14 +256,15 @@ peripheral_march_kernel(const PeriphBatch B) {
 
     double zc[8];                  // w . (y_k, F0 .. F6) of the current interval
     double inv_h = 0.0;
-    int slo = 0x7ff00000, shi = 0;
+    int slo = 0x7ff00000, shi = 0, slast = 0x3fe00000, sprev = 0x3fe00000;
     // f at local time s of the current interval, state xs
     auto rhs = [&](double s, double xs) {
         const double z = dense_eval(zc, s * inv_h);
         double sr, se;
         logistic_fast_parts(z, tab, sr, se);
         const double sg = fma(sr, se, sr);
-        slo = min(slo, __double2hiint(sg)); shi = max(shi, __double2hiint(sg));
+        slast = __double2hiint(sg);
+        slo = min(slo, slast); shi = max(shi, slast);
         return fma(vm, sg, -lam * xs);
     };
 
@@ -287,6 +293,7 @@ peripheral_march_kernel(const PeriphBatch B) {
         if (k == 0) {
             // first derivative and starting step (scalar form of the cost kernels' rule)
             k1 = rhs(0.0, x);
+            sprev = slast;
             const double sc = fma(rtol, fabs(x), atol);
             const double d0 = fabs(x) / sc, d1 = fabs(k1) / sc;
             const double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
@@ -302,7 +309,7 @@ peripheral_march_kernel(const PeriphBatch B) {
             double hs = h;
             bool hit = false;
             if (s + 1.01 * hs >= hk) { hs = hk - s; hit = true; }
-            slo = 0x7ff00000; shi = 0;
+            slo = sprev; shi = sprev;
             double K[D::kStages + 1];
             K[0] = k1;
 #pragma unroll
@@ -322,6 +329,7 @@ peripheral_march_kernel(const PeriphBatch B) {
                 xn = fma(hs, acc, x);
             }
             K[D::kStages] = rhs(hit ? hk : s + hs, xn);
+            const int snew = slast;
             double e5 = 0.0, e3 = 0.0;
 #pragma unroll
             for (int j = 0; j <= D::kStages; ++j) {
@@ -348,6 +356,7 @@ peripheral_march_kernel(const PeriphBatch B) {
                     ++nacc;
                     s = hit ? hk : s + hs;
                     x = xn;
+                    sprev = snew;
                     k1 = K[D::kStages];
                     float fac = fminf(LASSIM_FACMAX, fmaxf(0.2f, fac0));
                     if (rejected) fac = fminf(fac, 1.0f);

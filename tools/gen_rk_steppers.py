@@ -71,6 +71,9 @@ def emit(tb):
     w("//   sig(ys, sr, se)  evaluates the logistic terms sigmoid(W ys) = sr + sr*se for this lane's")
     w("//                genes (reciprocal seed and Newton residual, see logistic_fast_parts)")
     w("//   gmax(x)      max of a non-negative float over the lanes of the group")
+    w("//   s0, s1       high words of the logistic values at y (in) and at yn (out): the swing of")
+    w("//                the NEXT attempt starts from the state this one ends in, so that a switch")
+    w("//                before the first inner stage (c = %s) is seen as well" % ("%.3f" % C[1]))
     w("//   swing        jump guard (>= 2 switches it off).  The embedded estimates are blind to a")
     w("//                logistic term that switches early in the step (the stages there carry no")
     w("//                weight in the solution or its embedded companions): a term that swings by")
@@ -94,7 +97,7 @@ def emit(tb):
     w("        const double (&lam)[R], const double (&vm)[R], const double (&gr)[R],")
     w("        const double *tab, const double (&y)[R],")
     w("        const double (&k1)[R], const double hs, const double rtol, const double atol,")
-    w("        const float swing, double (&yn)[R], double (&kn)[R]) {")
+    w("        const float swing, const int (&s0)[R], int (&s1)[R], double (&yn)[R], double (&kn)[R]) {")
     decl = ", ".join("%s[R]" % k for k in K[1:S])
     w("    double %s;" % decl)
     w("    double ys[R], sg[R], sr[R], se[R], q[R], ly[R], cv[R], ef[R], ei[R], yz[R];")
@@ -103,7 +106,7 @@ def emit(tb):
     w("    int slo[R], shi[R];")
     w("#pragma unroll")
     w("    for (int r = 0; r < R; ++r) { ys[r] = fma(hs * %s, k1[r], y[r]); ef[r] = 1.0; ei[r] = 1.0;" % lit(A[1][0]))
-    w("                                  slo[r] = 0x7ff00000; shi[r] = 0; }")
+    w("                                  slo[r] = s0[r]; shi[r] = s0[r]; }")
     for s in range(2, S + 1):
         row = A[s] if s < S else B
         last = row[s - 1]
@@ -192,6 +195,7 @@ def emit(tb):
         w("    for (int r = 0; r < R; ++r) {")
         w("        kn[r] = fma(vm[r] * sr[r], se[r], fma(vm[r], sr[r], ly[r]));")
         w("        sg[r] = fma(sr[r], se[r], sr[r]);")
+        w("        s1[r] = __double2hiint(sg[r]);")
         w("    }")
     else:
         w("    sig(yn, sr, se);")
@@ -199,6 +203,7 @@ def emit(tb):
         w("    for (int r = 0; r < R; ++r) {")
         w("        kn[r] = fma(vm[r] * sr[r], se[r], fma(vm[r], sr[r], ly[r]));")
         w("        sg[r] = fma(sr[r], se[r], sr[r]);")
+        w("        s1[r] = __double2hiint(sg[r]);")
         w("    }")
         emit_measure()
     if nE == 1:
