@@ -637,7 +637,7 @@ def run_single(args, ctx):
     launches0 = eng.launch_count
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
-    kernel_ms, attempts, sp_ms, sp_att = [], [], [], []
+    kernel_ms, attempts, sp_ms, sp_att, rhs_evals = [], [], [], [], []
     ctx.barrier()
     for k in range(args.steps):
         ctx.flush.zero_()                      # evict L2 between timed steps
@@ -647,6 +647,7 @@ def run_single(args, ctx):
         ends[k].synchronize()
         kernel_ms.append(eng.last_kernel_ms())
         attempts.append(int(dcnt.view(POP, 3)[:, :2].sum().item()))
+        rhs_evals.append(int(dcnt.view(POP, 3)[:, 2].sum().item()))
         sp_ms.append(eng.last_stage_parallel_ms())            # the dominant kernel's own launch
         sp_att.append(eng.last_stage_parallel_attempts())
     ctx.barrier()
@@ -715,6 +716,12 @@ def run_single(args, ctx):
                 "same_costs_as_device_path": e2e_same},
         "gpu_launches": int(launches),
         "clocks": clocks,
+        # the same rate in the other units SURVEY.md 8d asks for (15 ODE solves per candidate;
+        # right-hand sides as counted by the kernels: 12 per attempt of the 8(5,3) pair, 6 of
+        # the 5(4) pair, 30 x warps of the stage-parallel pair)
+        "trajectories_per_s": 15 * value,
+        "rhs_evals_per_s": float(np.mean(rhs_evals)) * args.steps / (dev_ms * 1e-3),
+        "step_attempts_per_candidate": float(np.mean(attempts)) / POP,
         "roofline": roof,
         "other_integrator": other,
     }
