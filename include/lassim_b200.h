@@ -193,8 +193,9 @@ int lassim_trajectories(lassim_handle *h, int N, const double *X, double *Y,
  * core ONCE (8(5,3) pair with its 7th-order continuous extension, a hundred times
  * tighter than the candidates' tolerances; an error here means core_x has no
  * finite trajectory) and every candidate is a scalar equation driven by that
- * trajectory: one thread per candidate, same tolerances, error weight and
- * controller as everywhere.  lassim_set_peripheral_joint(h, 1) integrates the
+ * trajectory: one thread per candidate, the 8(5,3) pair whatever
+ * lassim_set_method says, same tolerances, error weight and controller as
+ * everywhere.  lassim_set_peripheral_joint(h, 1) integrates the
  * joint (n+1)-state system per candidate in the cost kernel instead (core of at
  * most 31 genes; 13x the work for the Th2 core; kept as a cross-check).
  *   genes    number of peripheral genes
