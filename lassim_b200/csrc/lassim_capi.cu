@@ -704,7 +704,10 @@ int build_core_table(lassim_handle *h) {
     DevProblem P{};
     P.n = n; P.T = T; P.K = 1; P.U = 0; P.dim = h->dim; P.nnz = h->nnz;
     P.times = h->d_times.p; P.y0 = h->d_y0.p; P.kidx = h->d_kidx.p;
-    P.max_steps = (unsigned int)(h->max_steps > 4000000000LL ? 4000000000LL : h->max_steps);
+    // the step budget of lassim_set_tolerances is per CANDIDATE; the one core solve gets the
+    // default budget at least (it is bounded by the table's capacity anyway)
+    const long long core_budget = h->max_steps > 20000000LL ? h->max_steps : 20000000LL;
+    P.max_steps = (unsigned int)(core_budget > 4000000000LL ? 4000000000LL : core_budget);
     P.swing = h->jump_guard;
     const size_t smem = ((size_t)kSmemHeader + nc + 2) * sizeof(double);
     CU(h->d_core_count.reserve(1));

@@ -190,3 +190,52 @@ def test_peripheral_genes_against_a_32_gene_core():
                                    sigma[g], y0[g], None, rtol=1e-13, atol=1e-13)
         assert cost[g] == pytest.approx(want, rel=1e-6)
     eng.close()
+
+
+def test_peripheral_edge_cases(th2):
+    """One sample time, repeated sample times, a one-gene core, degenerate and non-finite
+    candidates, a step budget, a change of tolerances: nothing hangs, failures are reported
+    per candidate, and what can be checked matches the definition."""
+    from lassim_b200 import Engine, LassimError
+    from lassim_b200._capi import ST_NONFINITE, ST_STEP_BUDGET
+    eng = Engine(0)
+    # a one-gene core, repeated sample times
+    times = np.array([0.0, 2.0, 2.0, 5.0])
+    maskc = np.ones(1, dtype=bool)
+    core_x = np.array([0.3, 0.8, 1.5])
+    eng.set_problem(np.zeros((4, 1)), np.ones(1), times, np.array([0.4]), maskc, None, 0.0)
+    data = np.array([[0.2, 0.5, 0.5, 1.0]]); sigma = np.array([0.3]); y0 = np.array([0.1])
+    eng.set_peripheral(core_x, data, sigma, y0, None)
+    Xp = np.array([[0.5, 1.0, 2.0], [0.0, 0.0, 0.0], [20.0, 20.0, -20.0], [0.5, np.nan, 1.0]])
+    cost, st = eng.eval_peripheral(0, Xp, return_status=True)
+    assert (st[:3] == 0).all() and (st[3] & ST_NONFINITE) and np.isnan(cost[3])
+    vmap = np.array([-1.0])
+    for i in range(3):
+        want = orc.peripheral_cost(Xp[i], core_x, times, np.array([0.4]), vmap, maskc, data[0],
+                                   sigma[0], y0[0], None, rtol=1e-13, atol=1e-13)
+        assert cost[i] == pytest.approx(want, rel=1e-6)
+    Y = eng.peripheral_trajectories(0, Xp[:1])
+    np.testing.assert_array_equal(Y[0, 1], Y[0, 2])          # the repeated sample time
+    # one sample time: nothing to integrate, cost of the initial state alone
+    eng.set_problem(np.zeros((1, 1)), np.ones(1), np.array([0.0]), np.array([0.4]), maskc, None, 0.0)
+    eng.set_peripheral(core_x, np.array([[0.7]]), sigma, y0, None)
+    assert eng.eval_peripheral(0, Xp[:1])[0] == pytest.approx((0.7 - 1.0) ** 2 / 0.09, rel=1e-12)
+    # Th2 core: step budget reported per candidate; tighter tolerances rebuild the core table
+    eng.set_problem(th2["data"], th2["sigma"], th2["times"], th2["y0"], th2["mask"], None, 0.0)
+    dataT, sigT, y0T, maskT, XT = peripheral_data(th2, 4)
+    eng.set_peripheral(mild_core(th2), dataT, sigT, y0T, maskT)
+    gene = np.arange(4, dtype=np.int32)
+    loose = eng.eval_peripheral(gene, XT)
+    eng.set_tolerances(1e-11, 1e-11)
+    tight = eng.eval_peripheral(gene, XT)
+    assert not np.array_equal(loose, tight)
+    np.testing.assert_allclose(loose, tight, rtol=1e-6)
+    eng.set_tolerances(max_steps=3)         # per candidate; the core solve keeps its own budget
+    cost, st = eng.eval_peripheral(gene, XT, return_status=True)
+    assert (st & ST_STEP_BUDGET).all() and np.isnan(cost).all()
+    eng.set_tolerances()
+    # a core that blows up is reported when the sweep is set up
+    bad = mild_core(th2).copy(); bad[0] = np.nan
+    with pytest.raises(LassimError, match="core"):
+        eng.set_peripheral(bad, dataT, sigT, y0T, maskT)
+    eng.close()
