@@ -740,6 +740,29 @@ def run_single(args, ctx):
     line["results_ok"] = bool(line["parity"]["ok"] and e2e_same)
     line["nonfinite_costs"] = len(line["parity"]["nan_rows_gpu"])
     line["async_islands"] = async_islands(ctx, eng, p)
+    # the N > 1 workload on this one GPU (one island of 1024, population seed 1000, DE on the
+    # device, no neighbour to migrate with): the like-for-like base of the multi-GPU lines
+    X0 = population(p, 1000)[None]
+    eng.de_init(X0, p["lb"], p["ub"], variant=DE_VARIANT, f=DE_F, cr=DE_CR, seed=42)
+    eng.de_set_island_ids(0, 1)
+    ext = torch.cuda.ExternalStream(eng.stream)
+    for _ in range(3):
+        eng.de_evolve(1)
+    torch.cuda.synchronize()
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0.record(ext)
+    for k in range(args.steps):
+        eng.de_evolve(1)
+        if (k + 1) % DE_GEN == 0:
+            eng.de_best()                 # what a migration reads; synchronises like one
+    a1.record(ext)
+    a1.synchronize()
+    arch_ms = a0.elapsed_time(a1)
+    line["archipelago_one_gpu"] = {
+        "value": POP * args.steps / (arch_ms * 1e-3), "ms_per_step": arch_ms / args.steps,
+        "note": "one island of 1024 evolving by DE on the device for `steps` generations (the "
+                "workload bench.py --gpus N times per GPU, without a neighbour): populations "
+                "that evolve hold other limit cycles than the fixed seed-0 population of `value`"}
     if not args.no_other_configs:
         line["other_configs"] = {}
         for c in (3, 4, 5):
