@@ -713,6 +713,8 @@ def run_single(args, ctx):
         "e2e": {"value": POP * args.steps / e2e_s, "unit": UNIT,
                 "h2d_bytes_per_step": int(X.nbytes), "d2h_bytes_per_step": int(POP * 8),
                 "api": "lassim_eval (C ABI) with pinned host X, host cost out",
+                "l2": "steps back to back, no flush (each step's X arrives from the host): the "
+                      "kernels' code and tables stay in L2, which `value`'s flushed steps reload",
                 "same_costs_as_device_path": e2e_same},
         "gpu_launches": int(launches),
         "clocks": clocks,
