@@ -312,7 +312,12 @@ void wide_dense(int method, KernelChoice *out) {
 }
 
 void wide_sparse(int method, int max_deg, KernelChoice *out) {
-    if (max_deg <= 8) {
+    if (max_deg <= 6) {
+        out->fn_capped = method == kMethodDOP853
+            ? grn_cost_kernel<64, 1, EllW<1, 6>, kMethodDOP853, true, false, false, true>
+            : grn_cost_kernel<64, 1, EllW<1, 6>, kMethodDP45, true, false, false, true>;
+        out->fn_wide = grn_series_pirk_wide_kernel<5, 2, EllW<1, 6>, true>;
+    } else if (max_deg <= 8) {
         out->fn_capped = method == kMethodDOP853
             ? grn_cost_kernel<64, 1, EllW<1, 8>, kMethodDOP853, true, false, false, true>
             : grn_cost_kernel<64, 1, EllW<1, 8>, kMethodDP45, true, false, false, true>;
@@ -329,6 +334,14 @@ void wide_sparse(int method, int max_deg, KernelChoice *out) {
 
 template <int L, int R>
 kernel_fn sparse_kernel(int method, int max_deg) {
+    // the two shapes of configs 3 and 4 (in-degree 5) also exist with 6 ELL slots per row:
+    // a quarter fewer loads and FMAs in the mat-vec than with 8, a dozen registers less
+    if constexpr ((L == 64 && R == 1) || (L == 128 && R == 2)) {
+        if (max_deg <= 6) {
+            if (method == kMethodDOP853) return grn_cost_kernel<L, R, EllW<R, 6>, kMethodDOP853, true>;
+            return grn_cost_kernel<L, R, EllW<R, 6>, kMethodDP45, true>;
+        }
+    }
     if (max_deg <= 8) {
         if (method == kMethodDOP853) return grn_cost_kernel<L, R, EllW<R, 8>, kMethodDOP853, true>;
         return grn_cost_kernel<L, R, EllW<R, 8>, kMethodDP45, true>;
@@ -351,6 +364,8 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
     const char *ex = getenv("LASSIM_EXACT_MATH");
     const bool fast = !(ex && atoi(ex) != 0);
     const int nc = (n + 3) & ~3;
+    const char *e8 = getenv("LASSIM_ELL8");               // A/B: 8 ELL slots also for in-degree <= 6
+    const int deg = (e8 && atoi(e8) != 0 && h->max_deg < 7) ? 7 : h->max_deg;
     if (n <= 12 && want == 4) {
         if (method == kMethodDP45)
             *out = {grn_cost_kernel<4, 3, DenseW<3, 12>, kMethodDP45, true>, 4, 3, "dense 4x3"};
@@ -392,10 +407,10 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
     // LASSIM_SPARSE_R2=1 brings the one-warp shape back (A/B).
     const char *r2 = getenv("LASSIM_SPARSE_R2");
     if (n <= 64) {
-        if (r2 && atoi(r2) != 0) *out = {sparse_kernel<32, 2>(method, h->max_deg), 32, 2, "sparse 32x2"};
+        if (r2 && atoi(r2) != 0) *out = {sparse_kernel<32, 2>(method, deg), 32, 2, "sparse 32x2"};
         else {
-            *out = {sparse_kernel<64, 1>(method, h->max_deg), 64, 1, "sparse 64x1"};
-            wide_sparse(method, h->max_deg, out);
+            *out = {sparse_kernel<64, 1>(method, deg), 64, 1, "sparse 64x1"};
+            wide_sparse(method, deg, out);
         }
         return true;
     }
@@ -405,11 +420,11 @@ bool choose_kernel(const lassim_handle *h, KernelChoice *out) {
     // barrier (70 genes: 128 x 2 -> 64 x 2 took a batch from 187 to 99 ms; 300 genes: 512 x 2 ->
     // 256 x 2 from 894 to 514 ms; 600 genes: 512 x 2 -> 384 x 2 from 750 to 618 ms; the
     // intermediate 96 and 192 gained 2-3 % and were left out)
-    if (n <= 128 && fine) { *out = {sparse_kernel<64, 2>(method, h->max_deg), 64, 2, "sparse 64x2"}; return true; }
-    if (n <= 256) { *out = {sparse_kernel<128, 2>(method, h->max_deg), 128, 2, "sparse 128x2"}; return true; }
-    if (n <= 512 && fine) { *out = {sparse_kernel<256, 2>(method, h->max_deg), 256, 2, "sparse 256x2"}; return true; }
-    if (n <= 768 && fine) { *out = {sparse_kernel<384, 2>(method, h->max_deg), 384, 2, "sparse 384x2"}; return true; }
-    if (n <= 1024) { *out = {sparse_kernel<512, 2>(method, h->max_deg), 512, 2, "sparse 512x2"}; return true; }
+    if (n <= 128 && fine) { *out = {sparse_kernel<64, 2>(method, deg), 64, 2, "sparse 64x2"}; return true; }
+    if (n <= 256) { *out = {sparse_kernel<128, 2>(method, deg), 128, 2, "sparse 128x2"}; return true; }
+    if (n <= 512 && fine) { *out = {sparse_kernel<256, 2>(method, deg), 256, 2, "sparse 256x2"}; return true; }
+    if (n <= 768 && fine) { *out = {sparse_kernel<384, 2>(method, deg), 384, 2, "sparse 384x2"}; return true; }
+    if (n <= 1024) { *out = {sparse_kernel<512, 2>(method, deg), 512, 2, "sparse 512x2"}; return true; }
     return false;
 }
 
