@@ -156,6 +156,12 @@ int lassim_trajectories_per_candidate(const lassim_handle *h);
  * over the candidate's trajectories.
  * Replaces N calls of CoreWithPerturbationsProblem._objfun_impl
  * (core_problem.py:134-155) / CoreProblem._objfun_impl (:75-92).
+ * pert_cost is the residual of min_a |a r - p|^2 (perturbation_functions.pyx:93-102)
+ * computed as p.p - (r.p)^2 / (r.r) with r scaled by its largest entry.  One deviation:
+ * where an end-state ratio overflows to -inf (a control state that decayed to 1e-190 under
+ * a knocked one of 1e120; one row in a thousand of a uniform Th2 population) the toolbox's
+ * numpy.linalg.lstsq raises LinAlgError; here the residual takes its limit for that
+ * entry -> -inf, p.p - p_k^2.  A NaN ratio gives a NaN cost, as there.
  */
 int lassim_eval(lassim_handle *h, int N, const double *X, double *cost,
                 double *cost_main, double *pert_cost, int *status,

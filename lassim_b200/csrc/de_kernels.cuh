@@ -118,7 +118,7 @@ __global__ void de_select_kernel(const DeParams p, double *__restrict__ X, doubl
     const int gi = p.ind_begin + li;
     if (gi >= p.ind_end) return;
     const double ft = Ft[li];
-    if (ft < F[gi]) {            // false for NaN: NaN never wins
+    if (ft < de_key(F[gi])) {    // false for a NaN trial: NaN never wins, and never stays
         F[gi] = ft;
         const double *t = trial + (size_t)gi * p.dim;
         double *x = X + (size_t)gi * p.dim;

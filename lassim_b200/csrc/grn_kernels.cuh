@@ -29,6 +29,19 @@
 #include <math_constants.h>
 #include <stdint.h>
 
+namespace lassim {
+// doubles of shared memory in front of the groups' exchange lines: the 2^(j/1024) table
+// (1024 entries + the two saturation entries 0 and 2^1000, padded to 1032) + 32 of
+// reduction / broadcast scratch for a CTA-wide group
+constexpr int kExpTable = 1024;
+constexpr int kExpTableLog2 = 10;
+constexpr int kTabDoubles = 1032;
+constexpr int kSmemHeader = kTabDoubles + 32;
+// 1.5 * 2^(52 - 10): adding it rounds to a multiple of 1/1024 and leaves that multiple in
+// the low word
+constexpr double kExpMagic = 6597069766656.0;
+}  // namespace lassim
+
 #include "rk_steppers.cuh"
 
 namespace lassim {
@@ -117,15 +130,8 @@ constexpr int min_blocks_for(int L) {
          : (L * LASSIM_MIN_BLOCKS_WIDE <= 1024 ? LASSIM_MIN_BLOCKS_WIDE : 1);
 }
 
-// doubles of shared memory in front of the groups' exchange lines: the 2^(j/256) table
-// (256 entries + the two saturation entries 0 and 2^1000, padded to 264) + 32 of
-// reduction / broadcast scratch for a CTA-wide group
-constexpr int kExpTable = 256;
-constexpr int kTabDoubles = 264;
-constexpr int kSmemHeader = kTabDoubles + 32;
-
-// 2^(j/256), j = 0..255, filled by the host when the engine is created.
-__constant__ double c_exp2_table[kExpTable];
+// 2^(j/1024), j = 0..1023, filled by the host when the engine is created.
+__device__ double g_exp2_table[kExpTable];
 
 // With the fast logistic the weights are pre-scaled by -log2(e), so the
 // mat-vec delivers t = -z*log2(e) directly.
@@ -138,14 +144,17 @@ __device__ __forceinline__ double logistic_libm(double z) {
     return 1.0 / (1.0 + exp(-z));
 }
 
-// 1 / (1 + 2^t), t = -z*log2(e).  With t = k + j/256 + f, |f| <= 2^-9:
-//   2^t = T[j] * g,  g = 2^k * (1 + f*p(f)),  p = degree-3 Taylor of (2^f - 1)/f
-// (truncation 4e-17), so the denominator is d = fma(T[j], g, 1).  The table value
-// comes out of shared memory last, so everything else - the polynomial, the
-// exponent scaling (on g, not on T[j]) - is arranged to be ready when it arrives:
-// one FMA separates the table load from d.  |t| >= 1000 (also NaN/inf) does not
-// go through a select after d either: it redirects the LOAD to one of two extra
-// table entries, T[256] = 0 (d = 1: 2^t vanishes next to 1) and T[257] = 2^1000
+// 1 / (1 + 2^t), t = -z*log2(e).  With t = k + j/1024 + f, |f| <= 2^-11:
+//   2^t = T[j] * g,  g = 2^k * (1 + f*(c1 + c2 f)),
+// the degree-2 polynomial with c1 moved off ln 2 so that the cubic remainder equioscillates
+// (relative error 1.6e-12, the size of the reciprocal's below; with the 256-entry table of
+// earlier rounds the same accuracy class took a degree-4 polynomial: three more FP64
+// instructions per gene and right-hand side and one more link in the chain).  The
+// denominator is d = fma(T[j], g, 1).  The table value comes out of shared memory last, so
+// everything else - the polynomial, the exponent scaling (on g, not on T[j]) - is arranged
+// to be ready when it arrives: one FMA separates the table load from d.  |t| >= 1000 (also
+// NaN/inf) does not go through a select after d either: it redirects the LOAD to one of two
+// extra table entries, T[1024] = 0 (d = 1: 2^t vanishes next to 1) and T[1025] = 2^1000
 // (result < 1e-301, where the reference returns vmax*exp(z) or 0 after overflow),
 // with g = 1; the test runs on the high word with integer ops beside the chain.
 // The reciprocal is an SFU seed r (MUFU.RCP64H, relative error <= 2^-20) and ONE
@@ -157,17 +166,13 @@ __device__ __forceinline__ void logistic_fast_parts(double t, const double *tab,
                                                     double &e) {
     const int thi = __double2hiint(t);
     const bool big = (thi & 0x7fffffff) >= 0x408f4000;
-    const double kMagic = 26388279066624.0;    // 1.5 * 2^44: ulp = 1/256
-    const double s = t + kMagic;
+    const double s = t + kExpMagic;
     const int ki = __double2loint(s);
-    const double f = t - (s - kMagic);
+    const double f = t - (s - kExpMagic);
     const int idx = big ? (thi < 0 ? kExpTable : kExpTable + 1) : (ki & (kExpTable - 1));
     const double tj = tab[idx];
-    const double f2 = f * f;
-    const double p01 = fma(0.2402265069591007, f, 0.6931471805599453);
-    const double p23 = fma(0.009618129107628477, f, 0.05550410866482158);
-    double g = fma(f, fma(f2, p23, p01), 1.0);
-    g = __hiloint2double(__double2hiint(g) + ((ki >> 8) << 20), __double2loint(g));
+    double g = fma(f, fma(0.24022650695910072, f, 0.6931471904848534), 1.0);
+    g = __hiloint2double(__double2hiint(g) + ((ki >> kExpTableLog2) << 20), __double2loint(g));
     if (big) g = 1.0;
     const double d = fma(tj, g, 1.0);
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
@@ -183,7 +188,7 @@ __device__ __forceinline__ double logistic_fast(double t, const double *tab) {
 // fills the table part of the shared-memory header (all threads of the CTA call it)
 __device__ __forceinline__ void fill_exp2_table(double *tab) {
     for (int i = threadIdx.x; i < kTabDoubles; i += blockDim.x)
-        tab[i] = (i < kExpTable) ? c_exp2_table[i]
+        tab[i] = (i < kExpTable) ? g_exp2_table[i]
                : (i == kExpTable + 1) ? 1.0715086071862673e301   // 2^1000
                                       : 0.0;
 }
@@ -848,7 +853,10 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                         rmax = G::max_group(rmax, gmask, red);
                         pp = G::sum_group(pp, gmask, red);
                         double rp = 0.0, rr2 = 0.0;
-                        const double inv = (rmax > 0.0) ? 1.0 / rmax : 0.0;
+                        // an infinite ratio (a control end state that decayed to 1e-190 under a knocked
+                        // one of 1e120): the limit of the residual, in which that entry alone counts
+                        const bool blown = rmax > 1.7e308;
+                        const double inv = blown ? 0.0 : (rmax > 0.0) ? 1.0 / rmax : 0.0;
                         for (int i = 0; i < n; ++i) {
                             const double *Es = B.E + ((size_t)c * P.K + 1 + P.U + i) * n;
                             const double *Ecn = B.E + ((size_t)c * P.K + P.knock_ctrl[i]) * n;
@@ -858,7 +866,7 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
                                     const int g = lg * R + r;
                                     double rr = __ldcg(Es + g) / __ldcg(Ecn + g) - 1.0;
                                     if (rr > 2.0) rr = 2.0;
-                                    rr *= inv;
+                                    rr = blown ? (fabs(rr) > 1.7e308 ? copysign(1.0, rr) : rr * 0.0) : rr * inv;
                                     const double p = P.pert[(size_t)i * np2 + g];
                                     rp = fma(rr, p, rp);
                                     rr2 = fma(rr, rr, rr2);

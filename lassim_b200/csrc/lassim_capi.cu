@@ -853,7 +853,7 @@ int lassim_create(int device, lassim_handle **out) {
     if (const char *sp = getenv("LASSIM_JUMP_GUARD")) h->jump_guard = (float)atof(sp);
     double tab[kExpTable];
     for (int j = 0; j < kExpTable; ++j) tab[j] = exp2((double)j / (double)kExpTable);
-    if (cudaMemcpyToSymbol(c_exp2_table, tab, sizeof(tab)) != cudaSuccess) {
+    if (cudaMemcpyToSymbol(g_exp2_table, tab, sizeof(tab)) != cudaSuccess) {
         lassim_destroy(h);
         return fail(nullptr, LASSIM_E_CUDA, "upload of the exp2 table failed");
     }

@@ -112,6 +112,7 @@ core_dense_kernel(const DevProblem P, const double *__restrict__ core_x, const C
     for (int ti = 1; ti < T && status == 0; ++ti) {
         const double tend = P.times[ti];
         while (status == 0) {
+            if (attempts >= P.max_steps) { status = 1; break; }
             double hs = h;
             bool hit = false;
             if (t + 1.01 * hs >= tend) { hs = tend - t; hit = true; }
@@ -201,7 +202,6 @@ core_dense_kernel(const DevProblem P, const double *__restrict__ core_x, const C
                 h = hs * fmax(0.2, fmin(fac0, 1.0));
                 if (!(fabs(h) > 1e-290) || t + h == t) status = 2;
             }
-            if (status == 0 && attempts >= P.max_steps) status = 1;
         }
     }
     if (g == 0) *out.count = status ? -1 - status : k;
@@ -305,6 +305,9 @@ peripheral_march_kernel(const PeriphBatch B) {
         }
         // sub-steps inside the interval; the warp stays together until all its lanes are through
         bool inside = live && st == 0 && hk > 0.0;
+        // (the budget is also checked here: an attempt that ends its interval leaves the loop
+        // below before the check there)
+        if (inside && nacc + nrej >= B.max_steps) { st |= 1; inside = false; }
         while (__any_sync(0xffffffffu, inside)) {
             double hs = h;
             bool hit = false;

@@ -571,14 +571,17 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
                     rmax = warp_max(rmax);
                     pp = warp_sum(pp);
                     double rp = 0.0, rr2 = 0.0;
-                    const double inv = (rmax > 0.0) ? 1.0 / rmax : 0.0;
+                    // an infinite ratio (a control end state that decayed to 1e-190 under a knocked
+                    // one of 1e120): the limit of the residual, in which that entry alone counts
+                    const bool blown = rmax > 1.7e308;
+                    const double inv = blown ? 0.0 : (rmax > 0.0) ? 1.0 / rmax : 0.0;
                     for (int i = 0; i < n; ++i) {
                         const double *Es = B.E + ((size_t)c * P.K + 1 + P.U + i) * n;
                         const double *Ecn = B.E + ((size_t)c * P.K + P.knock_ctrl[i]) * n;
                         if (ok) {
                             double rr = __ldcg(Es + g) / __ldcg(Ecn + g) - 1.0;
                             if (rr > 2.0) rr = 2.0;
-                            rr *= inv;
+                            rr = blown ? (fabs(rr) > 1.7e308 ? copysign(1.0, rr) : rr * 0.0) : rr * inv;
                             const double p = P.pert[(size_t)i * np2 + g];
                             rp = fma(rr, p, rp);
                             rr2 = fma(rr, rr, rr2);

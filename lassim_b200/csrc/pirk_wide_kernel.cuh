@@ -391,14 +391,16 @@ grn_series_pirk_wide_kernel(const DevProblem P, const DevBatch B) {
                     rmax = cta_fmax(rmax);
                     pp = cta_sum(pp);
                     double rp = 0.0, rr2 = 0.0;
-                    const double inv = (rmax > 0.0) ? 1.0 / rmax : 0.0;
+                    // an infinite ratio: the limit of the residual (see grn_cost_kernel)
+                    const bool blown = rmax > 1.7e308;
+                    const double inv = blown ? 0.0 : (rmax > 0.0) ? 1.0 / rmax : 0.0;
                     for (int i = 0; i < n; ++i) {
                         const double *Es = B.E + ((size_t)c * P.K + 1 + P.U + i) * n;
                         const double *Ecn = B.E + ((size_t)c * P.K + P.knock_ctrl[i]) * n;
                         if (ok) {
                             double rr = __ldcg(Es + g) / __ldcg(Ecn + g) - 1.0;
                             if (rr > 2.0) rr = 2.0;
-                            rr *= inv;
+                            rr = blown ? (fabs(rr) > 1.7e308 ? copysign(1.0, rr) : rr * 0.0) : rr * inv;
                             const double p = P.pert[(size_t)i * np2 + g];
                             rp = fma(rr, p, rp);
                             rr2 = fma(rr, rr, rr2);

@@ -216,11 +216,24 @@ def test_full_population_against_the_reference(engine, th2):
             sim[:, i * n:(i + 1) * n] = E[:, 3 + i] / E[:, u]
     sim -= 1.0
     sim[sim > 2] = 2
-    for c in range(0, len(X), 7):
+    blown = 0
+    for c in range(len(X)):
         if np.isfinite(sim[c]).all():
-            assert out["pert_cost"][c] == pytest.approx(orc.rank1_residual(sim[c], pflat), rel=1e-10)
+            if c % 7 == 0:
+                assert out["pert_cost"][c] == pytest.approx(orc.rank1_residual(sim[c], pflat), rel=1e-10)
+        elif np.isnan(sim[c]).any():
+            assert np.isnan(out["pert_cost"][c])
         else:
-            assert not np.isfinite(out["pert_cost"][c])
+            # a ratio that overflowed to -inf (numpy.linalg.lstsq raises there): the limit of the
+            # residual, in which the infinite entries alone count (include/lassim_b200.h)
+            k = np.isinf(sim[c])
+            want = pflat @ pflat - (np.sign(sim[c][k]) @ pflat[k]) ** 2 / k.sum()
+            assert out["pert_cost"][c] == pytest.approx(want, rel=1e-10)
+            assert rel(out["pert_cost"][c], g["ref_pert_cost"][c]) < 1e-2
+            blown += 1
+    if engine.method_name == "dop853":
+        assert blown >= 1      # row 798 of this population: the case stays covered
+    assert np.isfinite(out["cost"]).all()
     # the cost: reported
     ref_p, tight_p = g["ref_pert_cost"], g["tight_pert_cost"]
     pert_ok = rel(ref_p, tight_p) <= 1e-7

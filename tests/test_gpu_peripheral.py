@@ -233,6 +233,7 @@ def test_peripheral_edge_cases(th2):
     eng.set_tolerances(max_steps=3)         # per candidate; the core solve keeps its own budget
     cost, st = eng.eval_peripheral(gene, XT, return_status=True)
     assert (st & ST_STEP_BUDGET).all() and np.isnan(cost).all()
+    assert (eng.last_traj_steps(4)[:, 0] <= 3).all()         # and nobody went on past the budget
     eng.set_tolerances()
     # a core that blows up is reported when the sweep is set up
     bad = mild_core(th2).copy(); bad[0] = np.nan

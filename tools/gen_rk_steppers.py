@@ -232,19 +232,17 @@ def main():
              "    asm(\"rcp.approx.ftz.f64 %0, %1;\" : \"=d\"(r) : \"d\"(x));",
              "    return fma(r, fma(-x, r, 1.0), r);",
              "}", "",
-             "// 2^a for a >= 0 (clamped at 1000) with the kernel's 2^(j/256) table in shared memory:",
-             "// a = n + j/256 + f, |f| <= 2^-9, degree-3 Taylor of (2^f - 1)/f; exactly 1 for a = 0.",
+             "// 2^a for a >= 0 (clamped at 1000) with the kernel's 2^(j/1024) table in shared memory:",
+             "// a = n + j/1024 + f, |f| <= 2^-11, degree-2 Taylor of (2^f - 1)/f (5e-16); exactly 1 for a = 0.",
              "__device__ __forceinline__ double exp2_tab(double a, const double *tab) {",
              "    a = fmin(a, 1000.0);",
-             "    const double kMagic = 26388279066624.0;    // 1.5 * 2^44: ulp = 1/256",
-             "    const double s = a + kMagic;",
+             "    const double s = a + kExpMagic;",
              "    const int ki = __double2loint(s);",
-             "    const double f = a - (s - kMagic);",
-             "    const double tj = tab[ki & 255];",
-             "    const double p = fma(f * f, fma(0.009618129107628477, f, 0.05550410866482158),",
-             "                         fma(0.2402265069591007, f, 0.6931471805599453));",
+             "    const double f = a - (s - kExpMagic);",
+             "    const double tj = tab[ki & (kExpTable - 1)];",
+             "    const double p = fma(f, fma(0.05550410866482158, f, 0.24022650695910072), 0.6931471805599453);",
              "    const double v = fma(tj, f * p, tj);",
-             "    return __hiloint2double(__double2hiint(v) + ((ki >> 8) << 20), __double2loint(v));",
+             "    return __hiloint2double(__double2hiint(v) + ((ki >> kExpTableLog2) << 20), __double2loint(v));",
              "}", ""]
     parts.append(emit(dp45()))
     parts.append(emit(dop853()))
