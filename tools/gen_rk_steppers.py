@@ -1,7 +1,8 @@
 """Generates lassim_b200/csrc/rk_steppers.cuh: one fully unrolled step attempt
 per explicit Runge-Kutta pair (Dormand-Prince 5(4) and Dormand-Prince 8(5,3)).
 
-Why generated: the hot loop wants every coefficient as an immediate, zero
+Why generated: the hot loop wants every coefficient at a fixed place (a slot of
+one __constant__ array, read as an operand through a uniform register), zero
 coefficients skipped, and the terms of the next stage state that do not depend
 on the logistic being evaluated folded in advance (so that the dependent chain
 from the logistic to the next stage state is a single FMA).  Writing that out by
@@ -26,6 +27,25 @@ def lit(v):
     if "e" not in s and "." not in s and "inf" not in s:
         s += ".0"
     return s
+
+
+# A coefficient written as a literal costs two UMOV each time it is used (10-12 % of the executed
+# instructions of the explicit kernels, `ncu` source page): with RK_CONST_POOL (default on) they
+# live in a __constant__ array and arrive by one LDCU.64 each.  Measured: 16 Th2 populations 59.6 ->
+# 58.2 ms, config 4 (1024 candidates) 2499 -> 2437 ms, the lone limit cycles unchanged.  The same
+# change made the one-thread-per-candidate peripheral march 23 % SLOWER (8.4 -> 10.3 ms: nothing
+# there hides the load's latency), so dop853_dense_tables.cuh keeps its literals.
+USE_POOL = os.environ.get("RK_CONST_POOL", "1") != "0"
+POOL = []
+
+
+def con(v):
+    if not USE_POOL:
+        return lit(v)
+    v = float(v)
+    if v not in POOL:
+        POOL.append(v)
+    return "c_rk[%d]" % POOL.index(v)
 
 
 def dp45():
@@ -55,9 +75,9 @@ def weighted_sum(coefs, names, indent):
     terms = [(c, n) for c, n in zip(coefs, names) if c != 0.0]
     if not terms:
         return "0.0"
-    expr = "%s * %s[r]" % (lit(terms[0][0]), terms[0][1])
+    expr = "%s * %s[r]" % (con(terms[0][0]), terms[0][1])
     for c, n in terms[1:]:
-        expr = "fma(%s, %s[r], %s)" % (lit(c), n, expr)
+        expr = "fma(%s, %s[r], %s)" % (con(c), n, expr)
     return expr
 
 
@@ -105,7 +125,7 @@ def emit(tb):
     w("    // (monotonic for positive values; integer min/max keep this off the FP64 pipe)")
     w("    int slo[R], shi[R];")
     w("#pragma unroll")
-    w("    for (int r = 0; r < R; ++r) { ys[r] = fma(hs * %s, k1[r], y[r]); ef[r] = 1.0; ei[r] = 1.0;" % lit(A[1][0]))
+    w("    for (int r = 0; r < R; ++r) { ys[r] = fma(hs * %s, k1[r], y[r]); ef[r] = 1.0; ei[r] = 1.0;" % con(A[1][0]))
     w("                                  slo[r] = s0[r]; shi[r] = s0[r]; }")
     for s in range(2, S + 1):
         row = A[s] if s < S else B
@@ -113,11 +133,11 @@ def emit(tb):
         c = C[s - 1]
         target = "ys" if s < S else "yn"
         w("    {   // sigma at stage %d's state (c = %s) -> %s, %s" % (s, lit(c), K[s - 1], "state of stage %d" % (s + 1) if s < S else "solution"))
-        w("        const double hl = hs * %s;" % lit(last))
+        w("        const double hl = hs * %s;" % con(last))
         w("        if constexpr (IF) {")
         w("#pragma unroll")
         w("            for (int r = 0; r < R; ++r) {")
-        w("                ef[r] = exp2_tab(gr[r] * (hs * %s), tab);" % lit(c * 1.4426950408889634))
+        w("                ef[r] = exp2_tab(gr[r] * (hs * %s), tab);" % con(c * 1.4426950408889634))
         w("                ei[r] = (gr[r] == 0.0) ? 1.0 : fast_rcp(ef[r]);")
         w("                yz[r] = ef[r] * ys[r];")
         w("            }")
@@ -157,8 +177,8 @@ def emit(tb):
         w("        { const double base = %s;" % base)
         w("          const double eb = IF ? ef[r] * base : base;      // u-space sum mapped to y")
         if e_last != 0.0:
-            w("          ce%d[r] = (hs * %s) * vm[r];" % (m, lit(e_last)))
-            w("          eq%d[r] = fma(hs * %s, ly[r], eb); }" % (m, lit(e_last)))
+            w("          ce%d[r] = (hs * %s) * vm[r];" % (m, con(e_last)))
+            w("          eq%d[r] = fma(hs * %s, ly[r], eb); }" % (m, con(e_last)))
         else:
             w("          ce%d[r] = 0.0;" % m)
             w("          eq%d[r] = eb; }" % m)
@@ -244,8 +264,12 @@ def main():
              "    const double v = fma(tj, f * p, tj);",
              "    return __hiloint2double(__double2hiint(v) + ((ki >> kExpTableLog2) << 20), __double2loint(v));",
              "}", ""]
-    parts.append(emit(dp45()))
-    parts.append(emit(dop853()))
+    bodies = [emit(dp45()), emit(dop853())]
+    if POOL:
+        rows = [", ".join(lit(v) for v in POOL[i:i + 4]) for i in range(0, len(POOL), 4)]
+        parts.append("// tableau coefficients of both pairs (operands c[bank][offset] of the FP64 instructions)")
+        parts.append("__constant__ double c_rk[%d] = {\n    %s};\n" % (len(POOL), ",\n    ".join(rows)))
+    parts.extend(bodies)
     parts.append("}  // namespace lassim\n")
     with open(OUT, "w") as fh:
         fh.write("\n".join(parts))
