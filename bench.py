@@ -807,7 +807,9 @@ def run_archipelago(args, ctx):
 
     from lassim_b200.pygmo.migration import RingExchange
     exchange = RingExchange(ctx.dist if world > 1 else None, world, dim, delayed=not args.lockstep_migration)
-    warm = max(args.warmup, 3)
+    # at least two evolve rounds of warm-up: with the exchange one round behind, the second one
+    # is the first that applies a table (so nothing happens for the first time in the timed region)
+    warm = max(args.warmup, 3, 2 * DE_GEN)
     for k in range(warm):
         eng.de_evolve(1)
         if (k + 1) % DE_GEN == 0:

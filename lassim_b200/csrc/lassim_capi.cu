@@ -1462,6 +1462,10 @@ extern "C" int lassim_de_init(lassim_handle *h, int islands, int individuals, in
     CU(h->de_trial.reserve(count * dim));
     CU(h->de_F.reserve(count));
     CU(h->de_best.reserve((size_t)islands * (dim + 1)));
+    // room for the migration table of an archipelago of up to 64 islands (this handle's and the
+    // other ranks'): the first lassim_de_migrate_ring then allocates nothing - a cudaMalloc
+    // there would wait for whatever the device is running, a collective in flight included
+    CU(h->de_table.reserve((size_t)(islands > 64 ? islands : 64) * (dim + 1)));
     int rc;
     if ((rc = upload(h, h->de_lb, lb, dim))) return rc;
     if ((rc = upload(h, h->de_ub, ub, dim))) return rc;
