@@ -161,3 +161,20 @@ def test_context_and_args():
     assert args.num_islands >= 1
     opt = OptimizationFactory.new_base_optimization("DE")
     assert opt.handle_parameters(args) == {"gen": 2}
+
+
+@pytest.mark.parametrize("gen, header", [("gen_rk_steppers", "rk_steppers.cuh"),
+                                         ("gen_dop853_dense", "dop853_dense_tables.cuh")])
+def test_generated_headers_are_current(gen, header, tmp_path):
+    """The committed headers are what their generators write (tools/gen_*.py): nobody edited
+    one by hand or changed a generator without regenerating."""
+    import importlib.util
+    import os
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location(gen, os.path.join(repo, "tools", gen + ".py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    out = tmp_path / header
+    mod.main(str(out))
+    with open(os.path.join(repo, "lassim_b200", "csrc", header)) as fh:
+        assert out.read_text() == fh.read()

@@ -238,7 +238,7 @@ def emit(tb):
     return "\n".join(L)
 
 
-def main():
+def main(out=OUT):
     parts = ["// GENERATED by tools/gen_rk_steppers.py - do not edit by hand.",
              "// Fully unrolled step attempts of the explicit Runge-Kutta pairs used by",
              "// grn_cost_kernel.  Every stage state after the second is formed as",
@@ -271,9 +271,9 @@ def main():
         parts.append("__constant__ double c_rk[%d] = {\n    %s};\n" % (len(POOL), ",\n    ".join(rows)))
     parts.extend(bodies)
     parts.append("}  // namespace lassim\n")
-    with open(OUT, "w") as fh:
+    with open(out, "w") as fh:
         fh.write("\n".join(parts))
-    print("wrote", OUT)
+    print("wrote", out)
 
 
 if __name__ == "__main__":
