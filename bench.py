@@ -546,6 +546,7 @@ def roofline_dict(eng, N, peak, k_ms, d_ms, series_attempts, attempts):
             "note": "dominant kernel of the step: 2-3 limit-cycle time series of ~12,000 "
                     "sequential attempts each set its duration (latency-bound)",
             "evaluation": {"kernels": [eng.kernel_name + " (time series until handed over)",
+                                       "order_long_list_kernel (one CTA: hand-over list longest first)",
                                        eng.series_kernel_name(N),
                                        eng.kernel_name + " (knock-downs, second stream)"],
                            "ms": k_ms, "achieved": achieved_all,

@@ -888,6 +888,44 @@ grn_cost_kernel(const DevProblem P, const DevBatch B) {
     }
 }
 
+// Longest first.  The stage-parallel kernel behind the hand-over holds two time series per CTA
+// (296 at a time on 148 SMs); an evolving population hands over 450-650 of 1024 (the median
+// candidate then needs 900-1100 attempts), and in the order of arrival a limit cycle of 14,000
+// attempts may start in the second wave: evaluations of 27-30 ms where the longest time series
+// alone takes 22.  This kernel (one CTA, between the two launches on the same stream) reorders
+// the list by the attempts each entry still has ahead of it, estimated as (t_end - t) / h from
+// the state it was handed over with - a limit cycle keeps its small step, a trajectory on its
+// way to a steady state has long outgrown it.  Rank sort in shared memory; longer lists
+// (throughput-bound batches) are left as they are.  Changes the schedule, not a single result.
+constexpr int kOrderMax = 2048;
+__global__ void __launch_bounds__(1024)
+order_long_list_kernel(unsigned long long *__restrict__ list, const unsigned int *__restrict__ count,
+                       const double *__restrict__ t_at, const double *__restrict__ h_at,
+                       const double *__restrict__ times, int T) {
+    __shared__ float key[kOrderMax];
+    __shared__ unsigned long long ent[kOrderMax];
+    const unsigned n = *count;
+    if (n < 2u || n > (unsigned)kOrderMax) return;
+    const double t_end = times[T - 1];
+    for (unsigned i = threadIdx.x; i < n; i += blockDim.x) {
+        const unsigned long long e = list[i];
+        const unsigned c = (unsigned)(e & 0xffffffffull);
+        const double rem = (t_end - t_at[c]) / fmax(fabs(h_at[c]), 1e-300);
+        key[i] = (rem < 3.0e38) ? (float)rem : 3.0e38f;       // NaN or overflow: first
+        ent[i] = e;
+    }
+    __syncthreads();
+    for (unsigned i = threadIdx.x; i < n; i += blockDim.x) {
+        const float k = key[i];
+        unsigned rank = 0;
+        for (unsigned j = 0; j < n; ++j) {
+            const float kj = key[j];
+            rank += (kj > k || (kj == k && j < i)) ? 1u : 0u;
+        }
+        list[rank] = ent[i];
+    }
+}
+
 // Register-resident DFMA throughput probe (roofline denominator).
 __global__ void __launch_bounds__(256) fp64_probe_kernel(double *out, int iters,
                                                          double seed) {

@@ -97,6 +97,7 @@ struct lassim_handle {
     unsigned series_cap = 0;      // hand-over cap; 0 = automatic (series_cap_for)
     int handover_warps = 0;       // warps per trajectory of the kernel long time series move to; 0 = automatic
     int no_if = 0;                // LASSIM_NO_IF=1 (diagnostic): no integrating factor for growing genes
+    bool no_order = false;        // LASSIM_NO_ORDER=1 (A/B): the hand-over list in the order of arrival
     float jump_guard = 0.5f;      // lassim_set_jump_guard
     bool timed = false;
     std::string err, kernel_name, series_kernel_name;
@@ -544,6 +545,13 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
             // the cap of attempts continue in the multi-warp stage-parallel kernel behind it
             CU(launch(kc.fn_capped, threads, smem, kc.L, 0u, (unsigned)N, counters, s, series_cap_for(h, N), 0));
             if (time_it) CU(cudaEventRecord(h->ev_sp0, s));
+            if (!h->no_order) {
+                // longest first (order_long_list_kernel): one small CTA between the two
+                order_long_list_kernel<<<1, 1024, 0, s>>>(B.long_list, counters + 2, B.cost_main,
+                                                          B.pert_cost, P.times, P.T);
+                CU(cudaGetLastError());
+                h->launches += 1;
+            }
             if (wide)
                 CU(launch(kc.fn_wide, kc.wide_threads, kc.wide_smem, kc.wide_threads, 0u, (unsigned)N,
                           counters + 3, s, 0u, 1));
@@ -849,6 +857,7 @@ int lassim_create(int device, lassim_handle **out) {
     if (const char *sp = getenv("LASSIM_HANDOVER_WARPS")) h->handover_warps = atoi(sp);
     if (const char *sp = getenv("LASSIM_DE_LANES")) h->de_lanes_wanted = atoi(sp);
     if (const char *sp = getenv("LASSIM_NO_IF")) h->no_if = atoi(sp);
+    if (const char *sp = getenv("LASSIM_NO_ORDER")) h->no_order = atoi(sp) != 0;   // A/B: hand-over list as it arrives
     if (const char *sp = getenv("LASSIM_PERIPHERAL_JOINT")) h->periph_joint = atoi(sp) != 0;
     if (const char *sp = getenv("LASSIM_JUMP_GUARD")) h->jump_guard = (float)atof(sp);
     double tab[kExpTable];

@@ -218,16 +218,26 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
         return a + b2;
     };
 
+    // First item of trajectory slot q of CTA b: q * gridDim.x + b, later ones from the queue
+    // behind those.  With the hand-over list ordered longest first (order_long_list_kernel) the
+    // longest time series then sit on different SMs, each next to one from further down the
+    // list; taken from the queue, the two slots of a CTA would get neighbours of the list - the
+    // two limit cycles of a population on ONE SM, sharing schedulers to the end (+3 ms).
+    constexpr unsigned kSlots = THREADS / (32 * WARPS);
+    bool first_item = true;
     while (true) {
         unsigned w = 0;
-        if constexpr (DUAL) {
+        if (first_item) {
+            w = (unsigned)pairq * gridDim.x + blockIdx.x;
+            first_item = false;
+        } else if constexpr (DUAL) {
             if (role == 0 && lane == 0) *work_slot = atomicAdd(B.work_counter, 1u);
             pair_barrier();
-            w = *work_slot;
+            w = *work_slot + kSlots * gridDim.x;
             pair_barrier();            // both have read it before the next item overwrites it
         } else {
             if (lane == 0) w = atomicAdd(B.work_counter, 1u);
-            w = __shfl_sync(0xffffffffu, w, 0);
+            w = __shfl_sync(0xffffffffu, w, 0) + kSlots * gridDim.x;
         }
         // resume: the work items are the time series the kernel ahead of this one handed over
         const unsigned work_count = B.resume ? __ldcg(B.long_count) : B.work_count;
