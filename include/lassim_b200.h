@@ -349,6 +349,12 @@ int lassim_last_stage_parallel_attempts(lassim_handle *h, unsigned long long *at
  * counterpart.) */
 int lassim_last_stage_parallel_ms(lassim_handle *h, float *ms);
 
+/* Device time from the start of the last evaluation to the launch of its stage-parallel
+ * kernel in milliseconds: with the hand-over (mode 5) the phase in which every time series
+ * makes its first attempts in the standard kernel.  LASSIM_E_STATE as above.  (No reference
+ * counterpart.) */
+int lassim_last_capped_phase_ms(lassim_handle *h, float *ms);
+
 /* Number of kernels this handle has launched so far (an evaluation is one launch,
  * or two concurrent ones when speculation is active). */
 long long lassim_launch_count(const lassim_handle *h);

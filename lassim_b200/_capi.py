@@ -117,6 +117,8 @@ def load_library():
     lib.lassim_last_stage_parallel_attempts.restype = ctypes.c_int
     lib.lassim_last_stage_parallel_ms.argtypes = [H, ctypes.POINTER(ctypes.c_float)]
     lib.lassim_last_stage_parallel_ms.restype = ctypes.c_int
+    lib.lassim_last_capped_phase_ms.argtypes = [H, ctypes.POINTER(ctypes.c_float)]
+    lib.lassim_last_capped_phase_ms.restype = ctypes.c_int
     lib.lassim_stream.argtypes = [H]
     lib.lassim_stream.restype = ctypes.c_void_p
     lib.lassim_launch_count.argtypes = [H]
@@ -468,6 +470,15 @@ class Engine:
         ms = ctypes.c_float()
         self._check(self._lib.lassim_last_stage_parallel_ms(self._h, ctypes.byref(ms)),
                     "lassim_last_stage_parallel_ms")
+        return float(ms.value)
+
+    def last_capped_phase_ms(self):
+        """Device time from the start of the last evaluation to the launch of its
+        stage-parallel kernel (ms): the first attempts of every time series in the standard
+        kernel."""
+        ms = ctypes.c_float()
+        self._check(self._lib.lassim_last_capped_phase_ms(self._h, ctypes.byref(ms)),
+                    "lassim_last_capped_phase_ms")
         return float(ms.value)
 
     def series_kernel_name(self, N):

@@ -98,6 +98,8 @@ struct lassim_handle {
     int handover_warps = 0;       // warps per trajectory of the kernel long time series move to; 0 = automatic
     int no_if = 0;                // LASSIM_NO_IF=1 (diagnostic): no integrating factor for growing genes
     bool no_order = false;        // LASSIM_NO_ORDER=1 (A/B): the hand-over list in the order of arrival
+    bool knock_after_cap = false; // LASSIM_KNOCK_AFTER_CAP=1 (A/B): knock-down kernel behind the capped one
+    int knock_per_sm = 0;         // LASSIM_KNOCK_PER_SM=k (A/B): CTAs per SM of the knock-down kernel next to a hand-over
     float jump_guard = 0.5f;      // lassim_set_jump_guard
     bool timed = false;
     std::string err, kernel_name, series_kernel_name;
@@ -499,7 +501,7 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
     const bool speculate = series_fn != nullptr;
     auto launch = [&](kernel_fn fn, int threads, size_t smem, int lanes_per_item, unsigned begin,
                       unsigned count, unsigned int *counter, cudaStream_t st,
-                      unsigned series_cap = 0u, int resume = 0) -> cudaError_t {
+                      unsigned series_cap = 0u, int resume = 0, int cap_per_sm = 0) -> cudaError_t {
         if (count == 0) return cudaSuccess;
         const int items_per_cta = threads / lanes_per_item;
         cudaError_t e;
@@ -520,6 +522,8 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
         long long blocks = ((long long)count + items_per_cta - 1) / items_per_cta;
         const long long resident = (long long)h->sm_count * per_sm;
         if (blocks > resident) blocks = resident;
+        if (cap_per_sm > 0 && blocks > (long long)h->sm_count * cap_per_sm)
+            blocks = (long long)h->sm_count * cap_per_sm;
         if (blocks < 1) blocks = 1;
         DevBatch Bl = B;
         Bl.work_begin = begin; Bl.work_count = count; Bl.work_counter = counter;
@@ -536,7 +540,8 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
     if (time_it) h->sp_timed = false;
     if (speculate) {
         const unsigned rest = total - (unsigned)N;
-        if (rest > 0) {
+        const bool late_fork = h->knock_after_cap && smode == 5;
+        if (rest > 0 && !late_fork) {
             CU(cudaEventRecord(sc.ev_fork, s));
             CU(cudaStreamWaitEvent(sc.aux, sc.ev_fork, 0));
         }
@@ -545,6 +550,10 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
             // the cap of attempts continue in the multi-warp stage-parallel kernel behind it
             CU(launch(kc.fn_capped, threads, smem, kc.L, 0u, (unsigned)N, counters, s, series_cap_for(h, N), 0));
             if (time_it) CU(cudaEventRecord(h->ev_sp0, s));
+            if (rest > 0 && late_fork) {       // A/B: the knock-down kernel starts behind the capped one
+                CU(cudaEventRecord(sc.ev_fork, s));
+                CU(cudaStreamWaitEvent(sc.aux, sc.ev_fork, 0));
+            }
             if (!h->no_order) {
                 // longest first (order_long_list_kernel): one small CTA between the two
                 order_long_list_kernel<<<1, 1024, 0, s>>>(B.long_list, counters + 2, B.cost_main,
@@ -579,7 +588,8 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
             h->sp_timed = true;
         }
         if (rest > 0) {
-            CU(launch(kc.fn, threads, smem, kc.L, (unsigned)N, rest, counters + 1, sc.aux));
+            CU(launch(kc.fn, threads, smem, kc.L, (unsigned)N, rest, counters + 1, sc.aux, 0u, 0,
+                      smode == 5 ? h->knock_per_sm : 0));
             CU(cudaEventRecord(sc.ev_join, sc.aux));
             CU(cudaStreamWaitEvent(s, sc.ev_join, 0));
         }
@@ -857,7 +867,9 @@ int lassim_create(int device, lassim_handle **out) {
     if (const char *sp = getenv("LASSIM_HANDOVER_WARPS")) h->handover_warps = atoi(sp);
     if (const char *sp = getenv("LASSIM_DE_LANES")) h->de_lanes_wanted = atoi(sp);
     if (const char *sp = getenv("LASSIM_NO_IF")) h->no_if = atoi(sp);
-    if (const char *sp = getenv("LASSIM_NO_ORDER")) h->no_order = atoi(sp) != 0;   // A/B: hand-over list as it arrives
+    if (const char *sp = getenv("LASSIM_NO_ORDER")) h->no_order = atoi(sp) != 0;
+    if (const char *sp = getenv("LASSIM_KNOCK_AFTER_CAP")) h->knock_after_cap = atoi(sp) != 0;
+    if (const char *sp = getenv("LASSIM_KNOCK_PER_SM")) h->knock_per_sm = atoi(sp);
     if (const char *sp = getenv("LASSIM_PERIPHERAL_JOINT")) h->periph_joint = atoi(sp) != 0;
     if (const char *sp = getenv("LASSIM_JUMP_GUARD")) h->jump_guard = (float)atof(sp);
     double tab[kExpTable];
@@ -1366,6 +1378,17 @@ int lassim_last_stage_parallel_ms(lassim_handle *h, float *ms) {
     CU(guard_.err);
     CU(cudaEventSynchronize(h->ev_sp1));
     CU(cudaEventElapsedTime(ms, h->ev_sp0, h->ev_sp1));
+    return LASSIM_OK;
+}
+
+int lassim_last_capped_phase_ms(lassim_handle *h, float *ms) {
+    if (!h || !ms) return LASSIM_E_INVALID;
+    if (!h->sp_timed || !h->timed)
+        return fail(h, LASSIM_E_STATE, "the last evaluation did not launch the stage-parallel kernel");
+    DeviceGuard guard_(h->device);
+    CU(guard_.err);
+    CU(cudaEventSynchronize(h->ev_sp0));
+    CU(cudaEventElapsedTime(ms, h->ev0, h->ev_sp0));
     return LASSIM_OK;
 }
 

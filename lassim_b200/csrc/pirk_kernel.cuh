@@ -218,17 +218,19 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
         return a + b2;
     };
 
-    // First item of trajectory slot q of CTA b: q * gridDim.x + b, later ones from the queue
-    // behind those.  With the hand-over list ordered longest first (order_long_list_kernel) the
+    // First item of trajectory slot q of CTA b: q * gridDim.x + b (odd q: counted from the other
+    // end, q * gridDim.x + gridDim.x - 1 - b), later ones from the queue behind those.  With the hand-over list ordered longest first (order_long_list_kernel) the
     // longest time series then sit on different SMs, each next to one from further down the
     // list; taken from the queue, the two slots of a CTA would get neighbours of the list - the
-    // two limit cycles of a population on ONE SM, sharing schedulers to the end (+3 ms).
+    // two limit cycles of a population on ONE SM, sharing schedulers to the end (+3 ms).  The
+    // odd slots run backwards so that the longest entry shares its SM with the shortest of the
+    // first wave, or, when the list is shorter than the wave, with nobody.
     constexpr unsigned kSlots = THREADS / (32 * WARPS);
     bool first_item = true;
     while (true) {
         unsigned w = 0;
         if (first_item) {
-            w = (unsigned)pairq * gridDim.x + blockIdx.x;
+            w = (unsigned)pairq * gridDim.x + ((pairq & 1) ? gridDim.x - 1u - blockIdx.x : blockIdx.x);
             first_item = false;
         } else if constexpr (DUAL) {
             if (role == 0 && lane == 0) *work_slot = atomicAdd(B.work_counter, 1u);

@@ -4,6 +4,9 @@ import os, sys
 import numpy as np
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, REPO)
+from lassim_b200 import _capi
+if os.environ.get("LASSIM_LIB"):
+    _capi._LIB_PATH = os.path.join(REPO, "lassim_b200", os.environ["LASSIM_LIB"])
 from lassim_b200._capi import Engine
 p = dict(np.load(os.path.join(REPO, "tests", "golden", "th2_problem.npz")))
 for seed in (1000, 1003):
