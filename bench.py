@@ -537,7 +537,7 @@ def roofline_dict(eng, N, peak, k_ms, d_ms, series_attempts, attempts):
             "traffic": 581888,
             "traffic_source": "STATIC: one ncu --set full capture of this kernel on the same "
                               "workload (profiles/r2_y_ncu_full_summary.txt), not re-measured in "
-                              "this run; the evaluation's four kernels together read 2.37 MB and "
+                              "this run; the evaluation's kernels of an evaluation together read 2.37 MB and "
                               "write nothing back to DRAM, against 0.72 MB of X in + cost out: the "
                               "path is compute-bound",
             "kernel": eng.series_kernel_name(N), "kernel_ms": d_ms,
@@ -548,6 +548,7 @@ def roofline_dict(eng, N, peak, k_ms, d_ms, series_attempts, attempts):
             "evaluation": {"kernels": [eng.kernel_name + " (time series until handed over)",
                                        "order_long_list_kernel (one CTA: hand-over list longest first)",
                                        eng.series_kernel_name(N),
+                                       "start_gate_kernel (one thread: the second stream waits for the stage-parallel CTAs)",
                                        eng.kernel_name + " (knock-downs, second stream)"],
                            "ms": k_ms, "achieved": achieved_all,
                            "frac": achieved_all / peak if peak else None,

@@ -100,6 +100,7 @@ struct DevBatch {
     unsigned int *long_count = nullptr;        // zeroed before launch
     unsigned long long *long_list = nullptr;   // [N]
     unsigned long long *sp_attempts = nullptr; // attempts made by the stage-parallel kernel (sum)
+    unsigned int *started = nullptr;           // CTAs of the stage-parallel kernel that have begun to run
 };
 
 #ifndef LASSIM_FACMAX
@@ -924,6 +925,14 @@ order_long_list_kernel(unsigned long long *__restrict__ list, const unsigned int
         }
         list[rank] = ent[i];
     }
+}
+
+// Holds its stream until `expected` CTAs of the stage-parallel kernel behind a hand-over have
+// begun to run (they count themselves in *started): the knock-down kernel, next on that stream,
+// then finds them in place and fills what they leave (lassim_capi.cu, launch_kernels).  One
+// thread; the kernel it waits for was enqueued before it.
+__global__ void start_gate_kernel(const unsigned int *started, unsigned int expected) {
+    while (*reinterpret_cast<const volatile unsigned int *>(started) < expected) __nanosleep(500);
 }
 
 // Register-resident DFMA throughput probe (roofline denominator).

@@ -98,7 +98,8 @@ struct lassim_handle {
     int handover_warps = 0;       // warps per trajectory of the kernel long time series move to; 0 = automatic
     int no_if = 0;                // LASSIM_NO_IF=1 (diagnostic): no integrating factor for growing genes
     bool no_order = false;        // LASSIM_NO_ORDER=1 (A/B): the hand-over list in the order of arrival
-    bool knock_after_cap = false; // LASSIM_KNOCK_AFTER_CAP=1 (A/B): knock-down kernel behind the capped one
+    int knock_after_cap = -1;     // LASSIM_KNOCK_AFTER_CAP (A/B): 1 = the knock-down kernel starts when the
+                                  // stage-parallel kernel's CTAs are placed, 0 = at once, -1 = by batch size
     int knock_per_sm = 0;         // LASSIM_KNOCK_PER_SM=k (A/B): CTAs per SM of the knock-down kernel next to a hand-over
     float jump_guard = 0.5f;      // lassim_set_jump_guard
     bool timed = false;
@@ -228,7 +229,8 @@ struct ZeroLayout {
 
 ZeroLayout zero_layout(int N) {
     ZeroLayout z;
-    z.off_done = 32;       // [0,16): work counters and hand-over count, [16,24): stage-parallel attempts
+    z.off_done = 32;       // [0,16): work counters and hand-over count, [16,24): stage-parallel attempts,
+                           // [24,28): stage-parallel CTAs that have started (start_gate_kernel)
     z.off_status = z.off_done + sizeof(int) * (size_t)N;
     z.off_counters = (z.off_status + sizeof(int) * (size_t)N + 15) & ~(size_t)15;
     z.bytes = z.off_counters + sizeof(unsigned long long) * 3 * (size_t)N;
@@ -501,7 +503,8 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
     const bool speculate = series_fn != nullptr;
     auto launch = [&](kernel_fn fn, int threads, size_t smem, int lanes_per_item, unsigned begin,
                       unsigned count, unsigned int *counter, cudaStream_t st,
-                      unsigned series_cap = 0u, int resume = 0, int cap_per_sm = 0) -> cudaError_t {
+                      unsigned series_cap = 0u, int resume = 0, int cap_per_sm = 0,
+                      unsigned *blocks_out = nullptr) -> cudaError_t {
         if (count == 0) return cudaSuccess;
         const int items_per_cta = threads / lanes_per_item;
         cudaError_t e;
@@ -530,8 +533,9 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
         Bl.series_cap = series_cap; Bl.resume = resume; Bl.long_count = counters + 2;
         Bl.no_if = h->no_if;
         Bl.sp_attempts = reinterpret_cast<unsigned long long *>(counters + 4);
-        fn<<<(unsigned)blocks, threads, smem, st>>>(P, Bl);
         h->launches += 1;
+        if (blocks_out != nullptr) { *blocks_out = (unsigned)blocks; Bl.started = counters + 6; }
+        fn<<<(unsigned)blocks, threads, smem, st>>>(P, Bl);
         return cudaGetLastError();
     };
     const int threads = threads_for(kc.L);
@@ -540,7 +544,19 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
     if (time_it) h->sp_timed = false;
     if (speculate) {
         const unsigned rest = total - (unsigned)N;
-        const bool late_fork = h->knock_after_cap && smode == 5;
+        // Hand-over: the knock-down kernel starts when the capped kernel is through AND every CTA
+        // of the stage-parallel kernel behind it has begun to run (a one-thread gate kernel on
+        // the second stream waits for their count).  Started together with the capped kernel it
+        // doubles the time of the capped phase (its CTAs fill every SM beside one capped CTA:
+        // 2.95 against 1.48 ms for 1024 Th2 candidates) and then sits where the stage-parallel
+        // CTAs want to go; started behind the capped kernel by the event alone it gets there
+        // first (592 CTAs against 148 that need three slots each) and the long time series wait
+        // for it (+2 ms).  This way the time series have the machine while they are many, the
+        // stage-parallel CTAs get their SMs, and the knock-down CTAs fill what is left: 20.3 ->
+        // 19.4 ms (1024), 24.2 -> 21.3 (2048), 31.6 -> 27.3 (4096), 65.8 -> 64.3 (16,384).
+        // Batches below 64 keep the early start (8 candidates: 1.3 against 1.9 ms - nothing is
+        // handed over there and the two kernels would only run one after the other).
+        const bool late_fork = smode == 5 && (h->knock_after_cap < 0 ? N >= 64 : h->knock_after_cap != 0);
         if (rest > 0 && !late_fork) {
             CU(cudaEventRecord(sc.ev_fork, s));
             CU(cudaStreamWaitEvent(sc.aux, sc.ev_fork, 0));
@@ -550,7 +566,7 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
             // the cap of attempts continue in the multi-warp stage-parallel kernel behind it
             CU(launch(kc.fn_capped, threads, smem, kc.L, 0u, (unsigned)N, counters, s, series_cap_for(h, N), 0));
             if (time_it) CU(cudaEventRecord(h->ev_sp0, s));
-            if (rest > 0 && late_fork) {       // A/B: the knock-down kernel starts behind the capped one
+            if (rest > 0 && late_fork) {
                 CU(cudaEventRecord(sc.ev_fork, s));
                 CU(cudaStreamWaitEvent(sc.aux, sc.ev_fork, 0));
             }
@@ -561,15 +577,22 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
                 CU(cudaGetLastError());
                 h->launches += 1;
             }
+            unsigned sp_blocks = 0;
+            unsigned *gate = (rest > 0 && late_fork) ? &sp_blocks : nullptr;
             if (wide)
                 CU(launch(kc.fn_wide, kc.wide_threads, kc.wide_smem, kc.wide_threads, 0u, (unsigned)N,
-                          counters + 3, s, 0u, 1));
+                          counters + 3, s, 0u, 1, 0, gate));
             else if (handover_warps_for(h, N) == 3)
                 CU(launch(kc.fn_pirk3, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters + 3,
-                          s, 0u, 1));
+                          s, 0u, 1, 0, gate));
             else
                 CU(launch(kc.fn_pirk2, pirk_threads(2), kc.pirk2_smem, 64, 0u, (unsigned)N, counters + 3,
-                          s, 0u, 1));
+                          s, 0u, 1, 0, gate));
+            if (gate != nullptr) {
+                start_gate_kernel<<<1, 1, 0, sc.aux>>>(counters + 6, sp_blocks);
+                CU(cudaGetLastError());
+                h->launches += 1;
+            }
         } else if (smode == 1) {
             CU(launch(series_fn, threads, smem, 32, 0u, (unsigned)N, counters, s));
         } else {
@@ -868,7 +891,7 @@ int lassim_create(int device, lassim_handle **out) {
     if (const char *sp = getenv("LASSIM_DE_LANES")) h->de_lanes_wanted = atoi(sp);
     if (const char *sp = getenv("LASSIM_NO_IF")) h->no_if = atoi(sp);
     if (const char *sp = getenv("LASSIM_NO_ORDER")) h->no_order = atoi(sp) != 0;
-    if (const char *sp = getenv("LASSIM_KNOCK_AFTER_CAP")) h->knock_after_cap = atoi(sp) != 0;
+    if (const char *sp = getenv("LASSIM_KNOCK_AFTER_CAP")) h->knock_after_cap = atoi(sp);
     if (const char *sp = getenv("LASSIM_KNOCK_PER_SM")) h->knock_per_sm = atoi(sp);
     if (const char *sp = getenv("LASSIM_PERIPHERAL_JOINT")) h->periph_joint = atoi(sp) != 0;
     if (const char *sp = getenv("LASSIM_JUMP_GUARD")) h->jump_guard = (float)atof(sp);

@@ -141,6 +141,9 @@ grn_series_pirk_kernel(const DevProblem P, const DevBatch B) {
             else asm volatile("bar.sync 2, %0;" ::"n"(32 * WARPS) : "memory");
         }
     };
+    // this CTA runs: the knock-down kernel behind a hand-over waits until all of them do
+    // (start_gate_kernel)
+    if (threadIdx.x == 0 && B.started != nullptr) atomicAdd(B.started, 1u);
     fill_exp2_table(tab);
     for (int i = lane; i < PER_WARP; i += 32) fline[i] = 0.0;
     __syncthreads();

@@ -89,6 +89,7 @@ grn_series_pirk_wide_kernel(const DevProblem P, const DevBatch B) {
         return m;
     };
 
+    if (threadIdx.x == 0 && B.started != nullptr) atomicAdd(B.started, 1u);   // see grn_series_pirk_kernel
     fill_exp2_table(tab);
     for (int i = tid; i < 3 * S * NPAD; i += THREADS) fline[i] = 0.0;
     __syncthreads();
