@@ -251,9 +251,10 @@ int lassim_peripheral_trajectories(lassim_handle *h, int N, const int *gene,
  *                    `lanes` groups, each advancing through its generations on its own
  *                    stream with its own scratch; a slow candidate holds up its own
  *                    island's next generation only.  0 = automatic (one island per lane,
- *                    at most 16 lanes, while the islands hold at most 4096 individuals
- *                    together; lockstep beyond, where one batch per generation fills the
- *                    machine by itself); 1 = all islands in lockstep.  Up to 4096
+ *                    at most 16 lanes while the islands hold at most 1024 individuals
+ *                    together, at most 8 up to 2048, 4 up to 3072; lockstep beyond, where
+ *                    one batch per generation fills the machine by itself and lanes would
+ *                    take SMs from each other); 1 = all islands in lockstep.  Up to 4096
  *                    individuals the result does not depend on the number of lanes.
  *                    LASSIM_DE_LANES in the environment sets the initial value.
  */

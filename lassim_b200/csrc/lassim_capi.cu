@@ -504,7 +504,7 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
     auto launch = [&](kernel_fn fn, int threads, size_t smem, int lanes_per_item, unsigned begin,
                       unsigned count, unsigned int *counter, cudaStream_t st,
                       unsigned series_cap = 0u, int resume = 0, int cap_per_sm = 0,
-                      unsigned *blocks_out = nullptr) -> cudaError_t {
+                      unsigned *blocks_out = nullptr, bool spread = false) -> cudaError_t {
         if (count == 0) return cudaSuccess;
         const int items_per_cta = threads / lanes_per_item;
         cudaError_t e;
@@ -524,6 +524,10 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
         }
         long long blocks = ((long long)count + items_per_cta - 1) / items_per_cta;
         const long long resident = (long long)h->sm_count * per_sm;
+        // stage-parallel kernels (several trajectories per CTA, one CTA per SM): one trajectory
+        // per CTA for as long as there are SMs - two limit cycles packed into one CTA share its
+        // schedulers to the end (2 candidates: 26.3 ms against 19.1 for the slower one alone)
+        if (spread && blocks < resident) blocks = count < resident ? (long long)count : resident;
         if (blocks > resident) blocks = resident;
         if (cap_per_sm > 0 && blocks > (long long)h->sm_count * cap_per_sm)
             blocks = (long long)h->sm_count * cap_per_sm;
@@ -584,10 +588,10 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
                           counters + 3, s, 0u, 1, 0, gate));
             else if (handover_warps_for(h, N) == 3)
                 CU(launch(kc.fn_pirk3, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters + 3,
-                          s, 0u, 1, 0, gate));
+                          s, 0u, 1, 0, gate, true));
             else
                 CU(launch(kc.fn_pirk2, pirk_threads(2), kc.pirk2_smem, 64, 0u, (unsigned)N, counters + 3,
-                          s, 0u, 1, 0, gate));
+                          s, 0u, 1, 0, gate, true));
             if (gate != nullptr) {
                 start_gate_kernel<<<1, 1, 0, sc.aux>>>(counters + 6, sp_blocks);
                 CU(cudaGetLastError());
@@ -600,11 +604,14 @@ int launch_kernels(lassim_handle *h, const KernelChoice &kc, const DevProblem &P
             if (wide)
                 CU(launch(series_fn, kc.wide_threads, kc.wide_smem, kc.wide_threads, 0u, (unsigned)N, counters, s));
             else if (smode == 6)
-                CU(launch(series_fn, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters, s));
+                CU(launch(series_fn, pirk_threads(3), kc.pirk3_smem, 96, 0u, (unsigned)N, counters, s,
+                          0u, 0, 0, nullptr, true));
             else if (smode == 4)
-                CU(launch(series_fn, pirk_threads(2), kc.pirk2_smem, 64, 0u, (unsigned)N, counters, s));
+                CU(launch(series_fn, pirk_threads(2), kc.pirk2_smem, 64, 0u, (unsigned)N, counters, s,
+                          0u, 0, 0, nullptr, true));
             else
-                CU(launch(series_fn, pirk_threads(1), kc.pirk_smem, 32, 0u, (unsigned)N, counters, s));
+                CU(launch(series_fn, pirk_threads(1), kc.pirk_smem, 32, 0u, (unsigned)N, counters, s,
+                          0u, 0, 0, nullptr, true));
         }
         if (smode != 1 && time_it) {
             CU(cudaEventRecord(h->ev_sp1, s));
@@ -1472,18 +1479,20 @@ int de_evaluate_population(lassim_handle *h) {
 }
 
 // Lanes of the asynchronous evolve: `lanes` groups of consecutive islands, each with its own
-// stream and evaluation scratch.  Automatic: one island per lane up to 16 lanes while the
-// islands together hold at most 4096 individuals - there a generation of all of them is
-// over in the time of its slowest time series and lanes fill the wait (Th2, 20 generations:
-// 8 x 128 in lockstep 487 ms, in lanes 368 ms, one island alone 338 ms; 32 x 128: 822 / 727) -
-// and lockstep beyond, where one batch per generation keeps the machine full by itself
-// (8 x 1024: 912 ms in lockstep, 1265 ms in 8 lanes; tools/gpu_async_probe.py).
+// stream and evaluation scratch.  A generation of a small archipelago is over in the time of
+// its slowest time series, and lanes fill that wait; the fuller the machine is by one batch
+// per generation, the less there is to fill, and lanes then only take SMs from each other's
+// long time series.  Automatic (Th2, 10 generations, tools/gpu_lane_policy.py; ms in lockstep /
+// with the lanes chosen here): up to 1024 individuals in all one island per lane up to 16
+// (8 x 128: 205 / 169, 16 x 64: 169 / 133), up to 2048 at most 8 lanes (16 x 128: 234 / 211,
+// 32 x 64: 218 / 204), up to 3072 at most 4 (24 x 128: 269 / 260), lockstep beyond (32 x 128:
+// 300 against 389 in 16 lanes; 8 x 1024: 809 against 1338 in 8).
 int de_make_lanes(lassim_handle *h) {
     release_de_lanes(h);
     const int islands = h->de.islands;
-    const bool small = (long long)islands * h->de.np <= kBatchIndependentMax;
-    int lanes = h->de_lanes_wanted > 0 ? h->de_lanes_wanted
-              : small ? (islands < 16 ? islands : 16) : 1;
+    const long long total = (long long)islands * h->de.np;
+    const int most = total <= 1024 ? 16 : total <= 2048 ? 8 : total <= 3072 ? 4 : 1;
+    int lanes = h->de_lanes_wanted > 0 ? h->de_lanes_wanted : (islands < most ? islands : most);
     if (lanes > islands) lanes = islands;
     h->de_lanes.resize(lanes);
     for (int l = 0; l < lanes; ++l) {
