@@ -534,10 +534,10 @@ def roofline_dict(eng, N, peak, k_ms, d_ms, series_attempts, attempts):
     return {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
             "frac": achieved / peak if peak else None,
             # dram__bytes_read.sum + dram__bytes_write.sum of this kernel, per launch
-            "traffic": 882688,
+            "traffic": 521728,
             "traffic_source": "STATIC: one ncu --set full capture of this kernel on the same "
-                              "workload (profiles/r2_ab_ncu_full_summary.txt), not re-measured in "
-                              "this run; the evaluation's kernels of an evaluation together read 2.67 MB and "
+                              "workload (profiles/r2_ae_ncu_full_summary.txt), not re-measured in "
+                              "this run; the evaluation's kernels of an evaluation together read 2.31 MB and "
                               "write nothing back to DRAM, against 0.72 MB of X in + cost out: the "
                               "path is compute-bound",
             "kernel": eng.series_kernel_name(N), "kernel_ms": d_ms,
