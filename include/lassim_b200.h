@@ -124,8 +124,13 @@ int lassim_set_jump_guard(lassim_handle *h, double swing);
  *   5  hand-over: every time series starts in the standard kernel; those still
  *      going after a cap of attempts (lassim_set_series_cap) stop at the step they are
  *      on and continue in kernel 6 (kernel 4 above 8192 candidates), launched behind it
- *      on the same stream.  The many short time series stay cheap, the few long ones get
- *      the fast kernel almost to themselves
+ *      on the same stream, longest first (a one-CTA kernel in between orders the
+ *      hand-over list by the attempts each entry still has ahead of it), one trajectory
+ *      per CTA while SMs last.  The many short time series stay cheap, the few long ones
+ *      get the fast kernel almost to themselves.  In kernel 6 / 4 a time series continued
+ *      this way has its error estimate (the last correction of the iteration) scaled by
+ *      the rate at which the corrections shrink, rho / (1 - rho) within [0.1, 1]: the
+ *      last correction is the error of the iterate before the one that is kept
  *   2  automatic (default): 5 for batches of at most 16,384 candidates, else 0
  * Results are deterministic for a given mode and stay inside the same error control.
  * In the automatic mode a candidate's cost does not depend on the batch it is evaluated
@@ -133,7 +138,10 @@ int lassim_set_jump_guard(lassim_handle *h, double swing);
  * _objfun_impl) or inside a population it takes the same path and gets the same bits.
  * Larger batches are scheduled for throughput (the cap follows the batch size) and agree
  * at the level of the integration tolerance.  The knock-down trajectories always run on
- * the standard kernel, concurrently on a second stream.  (No reference counterpart.)
+ * the standard kernel, concurrently on a second stream; behind a hand-over (batches of 64
+ * and more) that kernel starts when the capped kernel is through and the CTAs of the
+ * stage-parallel kernel are in place (a one-thread gate kernel waits for them).
+ * (No reference counterpart.)
  * LASSIM_SPECULATE in the environment sets the initial mode. */
 int lassim_set_speculation(lassim_handle *h, int mode);
 
@@ -356,8 +364,9 @@ int lassim_last_stage_parallel_ms(lassim_handle *h, float *ms);
  * counterpart.) */
 int lassim_last_capped_phase_ms(lassim_handle *h, float *ms);
 
-/* Number of kernels this handle has launched so far (an evaluation is one launch,
- * or two concurrent ones when speculation is active). */
+/* Number of kernels this handle has launched so far (an evaluation is one launch, two
+ * concurrent ones with a speculative time-series kernel, five with the hand-over: capped
+ * kernel, list order, stage-parallel kernel, gate, knock-down kernel). */
 long long lassim_launch_count(const lassim_handle *h);
 
 /* The handle's own stream (a cudaStream_t as void*): what NULL selects in the _device
