@@ -71,31 +71,39 @@ class de:
         elif kind == 1:    # rand/1
             mutant = partner(0) + F * (partner(1) - partner(2))
         elif kind == 2:    # rand-to-best/1
-            mutant = X + F * (best - X) + F * (partner(0) - partner(1))
+            mutant = partner(0) - partner(1)
+            mutant += best
+            mutant -= X
+            mutant *= F
+            mutant += X
         elif kind == 3:    # best/2
             mutant = best + F * (partner(0) + partner(1) - partner(2) - partner(3))
         else:              # rand/2
             mutant = partner(4) + F * (partner(0) + partner(1) - partner(2) - partner(3))
-        if self.variant <= 5:
+        if self.cr >= 1.0:
+            # every draw succeeds: the whole mutant, whichever crossover (examples/
+            # optimization_de.json runs with CR = 1)
+            cross = None
+        elif self.variant <= 5:
             # exponential crossover: a run of consecutive components starting
             # at a random index: the first always, then one more for every
             # draw < CR until the first failure (pagmo's do/while; at most D)
             start = rng.integers(0, D, size=NP)
-            u = rng.random((NP, D))
-            stop = np.argmax(u >= self.cr, axis=1)
-            length = np.where((u >= self.cr).any(axis=1), 1 + stop, D)
-            length = np.minimum(length, D)
-            offs = (np.arange(D)[None, :] - start[:, None]) % D
+            fail = rng.random((NP, D)) >= self.cr
+            length = np.where(fail.any(axis=1), 1 + np.argmax(fail, axis=1), D)
+            np.minimum(length, D, out=length)
+            offs = np.arange(D)[None, :] - start[:, None]        # (j - start) mod D without %
+            offs[offs < 0] += D
             cross = offs < length[:, None]
         else:
             # binomial crossover: each component with probability CR, one forced
             cross = rng.random((NP, D)) < self.cr
             cross[np.arange(NP), rng.integers(0, D, size=NP)] = True
-        trial = np.where(cross, mutant, X)
-        out = (trial < lb) | (trial > ub)
-        if out.any():
-            redraw = rng.uniform(lb, ub, size=(NP, D))
-            trial = np.where(out, redraw, trial)
+        trial = mutant if cross is None else np.where(cross, mutant, X)
+        # components out of bounds are drawn again, uniformly inside them (only those)
+        rows, cols = np.nonzero((trial < lb) | (trial > ub))
+        if rows.size:
+            trial[rows, cols] = lb[cols] + rng.random(rows.size) * (ub[cols] - lb[cols])
         return trial
 
     @staticmethod
@@ -207,9 +215,9 @@ def _trials(pop, variant, F, CR):
     cross_bin[np.arange(NP), start] = True
     cross = np.where(exp_cross[:, None], cross_exp, cross_bin)
     trial = np.where(cross, mutant, X)
-    out = (trial < lb) | (trial > ub)
-    if out.any():
-        trial = np.where(out, rng.uniform(lb, ub, size=(NP, D)), trial)
+    rows, cols = np.nonzero((trial < lb) | (trial > ub))
+    if rows.size:
+        trial[rows, cols] = lb[cols] + rng.random(rows.size) * (ub[cols] - lb[cols])
     return trial
 
 
