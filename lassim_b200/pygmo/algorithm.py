@@ -101,9 +101,12 @@ class de:
             cross[np.arange(NP), rng.integers(0, D, size=NP)] = True
         trial = mutant if cross is None else np.where(cross, mutant, X)
         # components out of bounds are drawn again, uniformly inside them (only those)
-        rows, cols = np.nonzero((trial < lb) | (trial > ub))
-        if rows.size:
-            trial[rows, cols] = lb[cols] + rng.random(rows.size) * (ub[cols] - lb[cols])
+        trial = np.ascontiguousarray(trial)          # (it is: a fresh result) so that `flat` is a view
+        flat = trial.reshape(-1)
+        idx = np.flatnonzero((flat < np.tile(lb, NP)) | (flat > np.tile(ub, NP)))
+        if idx.size:
+            cols = idx % D
+            flat[idx] = lb[cols] + rng.random(idx.size) * (ub[cols] - lb[cols])
         return trial
 
     @staticmethod
